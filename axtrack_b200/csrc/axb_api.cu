@@ -1,0 +1,327 @@
+// C ABI of libaxtrack_b200.so (include/axtrack_b200.h): context, scratch management, launches.
+// No CPU fallback anywhere: every compute entry point needs a CUDA device.
+#include "axb_common.cuh"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+struct axb_ctx {
+    int device = 0;
+    int num_sms = 0;
+    std::string err;
+    int64_t launches = 0;
+    cudaStream_t own_stream = nullptr;
+
+    // device-side sticky status: [0] first input error key (atomicMin), [1] flag bits (atomicOr)
+    unsigned long long* status_dev = nullptr;
+    unsigned long long* status_host = nullptr;   // pinned
+
+    // K2
+    uint32_t* k2_scratch = nullptr;   int k2_scratch_ctas = 0;
+    int* work_counter = nullptr;
+    int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;
+    // K1
+    uint8_t* k1_scratch = nullptr;    size_t k1_scratch_bytes = 0;
+    // staging for the single-pair and host entry points
+    uint8_t* st_mask = nullptr;       size_t st_mask_bytes = 0;
+    uint32_t* st_bits = nullptr;      size_t st_bits_bytes = 0;
+    int32_t* st_dets = nullptr;       size_t st_dets_bytes = 0;
+    axb_pair_desc* st_pairs = nullptr; size_t st_pairs_bytes = 0;
+    int32_t* st_plen = nullptr;       size_t st_plen_bytes = 0;
+    uint8_t* st_unr = nullptr;        size_t st_unr_bytes = 0;
+    float* st_wc = nullptr;           size_t st_wc_bytes = 0;
+};
+
+namespace {
+
+bool cuda_ok(axb_ctx* c, cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return true;
+    char buf[512];
+    snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+    if (c) c->err = buf;
+    return false;
+}
+#define AXB_CUDA(c, call) do { if (!cuda_ok((c), (call), #call)) return AXB_ERR_CUDA; } while (0)
+
+int bad_arg(axb_ctx* c, const char* msg) { if (c) c->err = msg; return AXB_ERR_BAD_ARG; }
+
+template <class T>
+int grow(axb_ctx* c, T** ptr, size_t* have, size_t need) {
+    if (need <= *have && *ptr) return AXB_OK;
+    if (*ptr) { AXB_CUDA(c, cudaFree(*ptr)); *ptr = nullptr; *have = 0; }
+    size_t bytes = std::max<size_t>(need + need / 4, 256);
+    AXB_CUDA(c, cudaMalloc((void**)ptr, bytes));
+    *have = bytes;
+    return AXB_OK;
+}
+
+int ensure_k2(axb_ctx* c, int n_pairs) {
+    if (!c->k2_scratch) {
+        const size_t bytes = (size_t)c->num_sms * 4 * axb::kGCap * sizeof(uint32_t);
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_scratch, bytes));
+        c->k2_scratch_ctas = c->num_sms;
+    }
+    if (!c->work_counter) AXB_CUDA(c, cudaMalloc((void**)&c->work_counter, 256));
+    if (n_pairs + 1 > c->prefix_cap) {
+        if (c->prefix_dev) AXB_CUDA(c, cudaFree(c->prefix_dev));
+        c->prefix_dev = nullptr;
+        c->prefix_cap = std::max(n_pairs + 1, 1024) * 2;
+        AXB_CUDA(c, cudaMalloc((void**)&c->prefix_dev, (size_t)c->prefix_cap * sizeof(int)));
+    }
+    return AXB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* axb_version(void) { return "axtrack_b200 0.1 (sm_100a)"; }
+
+int axb_create(int device, axb_ctx** out) {
+    if (!out) return AXB_ERR_BAD_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return AXB_ERR_CUDA;
+    axb_ctx* c = new axb_ctx();
+    c->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete c; return AXB_ERR_CUDA; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete c; return AXB_ERR_CUDA; }
+    c->num_sms = prop.multiProcessorCount;
+    if (cudaMalloc((void**)&c->status_dev, 2 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMallocHost((void**)&c->status_host, 2 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete c; return AXB_ERR_CUDA;
+    }
+    c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
+    if (cudaMemcpy(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice) != cudaSuccess) { delete c; return AXB_ERR_CUDA; }
+    *out = c;
+    return AXB_OK;
+}
+
+void axb_destroy(axb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    cudaFree(c->status_dev); cudaFreeHost(c->status_host);
+    cudaFree(c->k2_scratch); cudaFree(c->work_counter); cudaFree(c->prefix_dev); cudaFree(c->k1_scratch);
+    cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
+    cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+const char* axb_last_error(const axb_ctx* c) { return c ? c->err.c_str() : "no context"; }
+int64_t axb_launch_count(const axb_ctx* c) { return c ? c->launches : 0; }
+int axb_mask_words(int W) { return (W + 31) / 32; }
+
+int axb_pack_mask(axb_ctx* c, const uint8_t* mask_dev, int n_masks, int H, int W,
+                  uint32_t* mask_bits_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (!mask_dev || !mask_bits_dev || n_masks < 0 || H <= 0 || W <= 0) return bad_arg(c, "axb_pack_mask: bad argument");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    axb::launch_pack_mask_u8(mask_dev, n_masks, H, W, mask_bits_dev, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
+int axb_pack_weights(axb_ctx* c, const float* weights_dev, int n_masks, int H, int W,
+                     uint32_t* mask_bits_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (!weights_dev || !mask_bits_dev || n_masks < 0 || H <= 0 || W <= 0) return bad_arg(c, "axb_pack_weights: bad argument");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    axb::launch_pack_mask_f32(weights_dev, n_masks, H, W, mask_bits_dev, c->status_dev + 1, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
+int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
+                          const int32_t* dets_yx_dev, const axb_pair_desc* pairs_dev, int n_pairs,
+                          int total_src, int max_px,
+                          int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_pairs < 0 || total_src < 0 || H <= 0 || W <= 0 || n_masks <= 0) return bad_arg(c, "axb_cost_matrix_batch: bad size");
+    if (max_px < 1 || max_px > AXB_MAX_PX) return bad_arg(c, "axb_cost_matrix_batch: max_px outside [1, AXB_MAX_PX]");
+    if (n_pairs == 0 || total_src == 0) return AXB_OK;
+    if (!mask_bits_dev || !dets_yx_dev || !pairs_dev || !path_len_dev || !unreachable_dev)
+        return bad_arg(c, "axb_cost_matrix_batch: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = ensure_k2(c, n_pairs);
+    if (rc != AXB_OK) return rc;
+    AXB_CUDA(c, cudaMemsetAsync(c->work_counter, 0, sizeof(int), s));
+    axb::launch_work_prefix(pairs_dev, n_pairs, c->prefix_dev, s);
+    c->last_n_pairs = n_pairs;
+    axb::K2Params p;
+    p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = (W + 31) / 32;
+    p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs; p.work_prefix = c->prefix_dev;
+    p.max_px = max_px; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
+    p.scratch = c->k2_scratch; p.work_counter = c->work_counter; p.err_key = c->status_dev;
+    const int grid = std::max(1, std::min(c->k2_scratch_ctas, total_src));
+    axb::launch_k2(p, grid, s);
+    c->launches += 2;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
+int axb_cost_matrix(axb_ctx* c, const uint32_t* mask_bits_dev, int H, int W,
+                    const int32_t* src_yx_dev, int n_src, const int32_t* dst_yx_dev, int n_dst,
+                    int max_px, int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev,
+                    void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_src < 0 || n_dst < 0) return bad_arg(c, "axb_cost_matrix: negative count");
+    if (n_src == 0 || n_dst == 0) return AXB_OK;
+    if (!src_yx_dev || !dst_yx_dev) return bad_arg(c, "axb_cost_matrix: NULL detections");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = grow(c, &c->st_dets, &c->st_dets_bytes, (size_t)(n_src + n_dst) * 8);
+    if (rc != AXB_OK) return rc;
+    rc = grow(c, &c->st_pairs, &c->st_pairs_bytes, sizeof(axb_pair_desc));
+    if (rc != AXB_OK) return rc;
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_dets, src_yx_dev, (size_t)n_src * 8, cudaMemcpyDeviceToDevice, s));
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_dets + 2 * (size_t)n_src, dst_yx_dev, (size_t)n_dst * 8, cudaMemcpyDeviceToDevice, s));
+    axb_pair_desc pd;
+    memset(&pd, 0, sizeof pd);
+    pd.mask_idx = 0; pd.src_off = 0; pd.n_src = n_src; pd.dst_off = n_src; pd.n_dst = n_dst; pd.out_off = 0;
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, &pd, sizeof pd, cudaMemcpyHostToDevice, s));   // pageable source: staged before return
+    return axb_cost_matrix_batch(c, mask_bits_dev, 1, H, W, c->st_dets, c->st_pairs, 1, n_src, max_px,
+                                 path_len_dev, unreachable_dev, wcost_dev, stream);
+}
+
+int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_masks, int H, int W,
+                               const int32_t* dets_yx_host, int n_dets,
+                               const axb_pair_desc* pairs_host, int n_pairs, int max_px,
+                               int32_t* path_len_host, uint8_t* unreachable_host, float* wcost_host) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_pairs < 0 || n_dets < 0 || n_masks <= 0 || H <= 0 || W <= 0) return bad_arg(c, "axb_cost_matrix_batch_host: bad size");
+    if (n_pairs == 0) return AXB_OK;
+    if (!masks_host || !pairs_host || !path_len_host || !unreachable_host || (n_dets > 0 && !dets_yx_host))
+        return bad_arg(c, "axb_cost_matrix_batch_host: NULL pointer");
+    long long total_out = 0; long long total_src = 0;
+    for (int i = 0; i < n_pairs; ++i) {
+        const axb_pair_desc& pd = pairs_host[i];
+        if (pd.n_src < 0 || pd.n_dst < 0 || pd.src_off < 0 || pd.dst_off < 0 || pd.src_off + pd.n_src > n_dets ||
+            pd.dst_off + pd.n_dst > n_dets || pd.mask_idx < 0 || pd.mask_idx >= n_masks || pd.out_off < 0)
+            return bad_arg(c, "axb_cost_matrix_batch_host: pair descriptor out of range");
+        total_out = std::max(total_out, (long long)pd.out_off + (long long)pd.n_src * pd.n_dst);
+        total_src += pd.n_src;
+    }
+    if (total_src > 0x7fffffffLL) return bad_arg(c, "axb_cost_matrix_batch_host: too many sources");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = c->own_stream;
+    const size_t mask_bytes = (size_t)n_masks * H * W;
+    const size_t bits_bytes = (size_t)n_masks * H * ((W + 31) / 32) * 4;
+    int rc;
+    if ((rc = grow(c, &c->st_mask, &c->st_mask_bytes, mask_bytes)) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_bits, &c->st_bits_bytes, bits_bytes)) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_dets, &c->st_dets_bytes, (size_t)std::max(n_dets, 1) * 8)) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_pairs, &c->st_pairs_bytes, (size_t)n_pairs * sizeof(axb_pair_desc))) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_plen, &c->st_plen_bytes, (size_t)std::max(total_out, 1LL) * 4)) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_unr, &c->st_unr_bytes, (size_t)std::max(total_out, 1LL))) != AXB_OK) return rc;
+    if (wcost_host && (rc = grow(c, &c->st_wc, &c->st_wc_bytes, (size_t)std::max(total_out, 1LL) * 4)) != AXB_OK) return rc;
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_mask, masks_host, mask_bytes, cudaMemcpyHostToDevice, s));
+    if (n_dets > 0) AXB_CUDA(c, cudaMemcpyAsync(c->st_dets, dets_yx_host, (size_t)n_dets * 8, cudaMemcpyHostToDevice, s));
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, pairs_host, (size_t)n_pairs * sizeof(axb_pair_desc), cudaMemcpyHostToDevice, s));
+    if ((rc = axb_pack_mask(c, c->st_mask, n_masks, H, W, c->st_bits, s)) != AXB_OK) return rc;
+    if (total_out > 0 && total_src > 0) {
+        rc = axb_cost_matrix_batch(c, c->st_bits, n_masks, H, W, c->st_dets, c->st_pairs, n_pairs, (int)total_src,
+                                   max_px, c->st_plen, c->st_unr, wcost_host ? c->st_wc : nullptr, s);
+        if (rc != AXB_OK) return rc;
+        AXB_CUDA(c, cudaMemcpyAsync(path_len_host, c->st_plen, (size_t)total_out * 4, cudaMemcpyDeviceToHost, s));
+        AXB_CUDA(c, cudaMemcpyAsync(unreachable_host, c->st_unr, (size_t)total_out, cudaMemcpyDeviceToHost, s));
+        if (wcost_host) AXB_CUDA(c, cudaMemcpyAsync(wcost_host, c->st_wc, (size_t)total_out * 4, cudaMemcpyDeviceToHost, s));
+    }
+    AXB_CUDA(c, cudaStreamSynchronize(s));
+    return AXB_OK;
+}
+
+int axb_cost_matrix_host(axb_ctx* c, const uint8_t* mask_host, int H, int W,
+                         const int32_t* src_yx_host, int n_src, const int32_t* dst_yx_host, int n_dst,
+                         int max_px, int32_t* path_len_host, uint8_t* unreachable_host, float* wcost_host) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_src < 0 || n_dst < 0) return bad_arg(c, "axb_cost_matrix_host: negative count");
+    if (n_src == 0 || n_dst == 0) return AXB_OK;
+    if (!src_yx_host || !dst_yx_host) return bad_arg(c, "axb_cost_matrix_host: NULL detections");
+    std::vector<int32_t> dets((size_t)(n_src + n_dst) * 2);
+    memcpy(dets.data(), src_yx_host, (size_t)n_src * 8);
+    memcpy(dets.data() + 2 * (size_t)n_src, dst_yx_host, (size_t)n_dst * 8);
+    axb_pair_desc pd;
+    memset(&pd, 0, sizeof pd);
+    pd.n_src = n_src; pd.dst_off = n_src; pd.n_dst = n_dst;
+    return axb_cost_matrix_batch_host(c, mask_host, 1, H, W, dets.data(), n_src + n_dst, &pd, 1, max_px,
+                                      path_len_host, unreachable_host, wcost_host);
+}
+
+int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
+                   int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist, int cap,
+                   float* pre_conf_dev, int32_t* pre_xy_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
+                   float* conf_dev, int32_t* xy_dev, int32_t* keep_idx_dev, int32_t* n_out_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (F < 0 || ntiles <= 0 || Sx <= 0 || Sy <= 0 || tilesize <= 0 || cap <= 0 || nms_dist < 0 || nms_dist > 30000)
+        return bad_arg(c, "axb_decode_nms: bad size");
+    if (F == 0) return AXB_OK;
+    if (!Y_dev || !tile_yx_dev || !n_pre_dev || !conf_dev || !xy_dev || !keep_idx_dev || !n_out_dev)
+        return bad_arg(c, "axb_decode_nms: NULL pointer");
+    const long long ncell_ll = (long long)ntiles * Sx * Sy;
+    if (ncell_ll > (1 << 24)) return bad_arg(c, "axb_decode_nms: more than 2^24 grid cells per frame");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    const int ncell = (int)ncell_ll;
+    int npad = 1;
+    while (npad < ncell) npad <<= 1;
+    const size_t per_frame = axb::k1_scratch_per_frame(ncell, npad);
+    int rc = grow(c, &c->k1_scratch, &c->k1_scratch_bytes, per_frame * (size_t)F);
+    if (rc != AXB_OK) return rc;
+    axb::K1Params p;
+    p.Y = Y_dev; p.tile_yx = tile_yx_dev; p.F = F; p.ntiles = ntiles; p.Sx = Sx; p.Sy = Sy; p.tilesize = tilesize;
+    p.conf_thr = conf_thr; p.nms_d2 = nms_dist * nms_dist; p.cap = cap;
+    p.pre_conf = pre_conf_dev; p.pre_xy = pre_xy_dev; p.pre_tile = pre_tile_dev; p.n_pre = n_pre_dev;
+    p.conf = conf_dev; p.xy = xy_dev; p.keep_idx = keep_idx_dev; p.n_out = n_out_dev;
+    p.scratch = c->k1_scratch; p.scratch_per_frame = per_frame; p.npad = npad; p.err_flags = c->status_dev + 1;
+    axb::launch_k1(p, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
+int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    AXB_CUDA(c, cudaMemcpyAsync(c->status_host, c->status_dev, 16, cudaMemcpyDeviceToHost, s));
+    AXB_CUDA(c, cudaStreamSynchronize(s));
+    const unsigned long long key = c->status_host[0], flags = c->status_host[1];
+    if (info) { info[0] = info[1] = info[2] = -1; }
+    int rc = AXB_OK;
+    if (flags & 1ull) rc = AXB_ERR_BAD_WEIGHT;                       // checked first by the reference (astar_wrapper.py:35)
+    else if (key != ~0ull) {
+        const int code = (int)(key & 3ull);
+        const long long j = (long long)((key >> 2) & 0xFFFFFFull);
+        const long long item = (long long)(key >> 26);
+        rc = code == 1 ? AXB_ERR_OOB_START : AXB_ERR_OOB_GOAL;
+        if (info) {
+            info[2] = j; info[0] = -1; info[1] = item;
+            const int n = c->last_n_pairs;
+            if (n > 0 && c->prefix_dev) {
+                std::vector<int> pre((size_t)n + 1);
+                AXB_CUDA(c, cudaMemcpy(pre.data(), c->prefix_dev, ((size_t)n + 1) * sizeof(int), cudaMemcpyDeviceToHost));
+                int lo = (int)(std::upper_bound(pre.begin(), pre.begin() + n, (int)item) - pre.begin()) - 1;
+                lo = std::max(lo, 0);
+                info[0] = lo; info[1] = item - pre[lo];
+            }
+        }
+    }
+    else if (flags & 2ull) rc = AXB_ERR_UNSUPPORTED_WEIGHT;
+    else if (flags & 4ull) rc = AXB_ERR_CAPACITY;
+    if (key != ~0ull || flags) {
+        c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
+        AXB_CUDA(c, cudaMemcpyAsync(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice, s));
+        AXB_CUDA(c, cudaStreamSynchronize(s));
+    }
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,202 @@
+"""torch-facing wrappers of the C ABI: tensors in, tensors out, on torch's current stream.
+
+PyTorch is used for device memory and streams only; all arithmetic happens in
+libaxtrack_b200.so.  Every function here requires CUDA tensors and fails loudly otherwise.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_contexts = {}
+
+
+def get_context(device=None):
+    """The cached axb context of a CUDA device (default: torch's current device)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError('axtrack_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback')
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    if idx not in _contexts:
+        _contexts[idx] = _lib.Context(idx)
+    return _contexts[idx]
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(t, name, dtype=None):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f'{name} must be a CUDA tensor')
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f'{name} must have dtype {dtype}, got {t.dtype}')
+    return t.contiguous()
+
+
+def mask_words(W):
+    return (int(W) + 31) // 32
+
+
+def pack_mask(mask):
+    """uint8/bool CUDA tensor [H,W] or [n,H,W] (value 1 = on mask) -> int32 [n,H,ceil(W/32)].
+
+    Replaces AxonDetections._get_maskweights (AxonDetections.py:587-598)."""
+    if mask.dtype == torch.bool:
+        mask = mask.view(torch.uint8)
+    mask = _need_cuda(mask, 'mask', torch.uint8)
+    if mask.dim() == 2:
+        mask = mask.unsqueeze(0)
+    n, H, W = mask.shape
+    ctx = get_context(mask.device)
+    bits = torch.empty((n, H, mask_words(W)), dtype=torch.int32, device=mask.device)
+    ctx.check(ctx.lib.axb_pack_mask(ctx.handle, mask.data_ptr(), n, H, W, bits.data_ptr(), _stream()))
+    return bits
+
+
+def pack_weights(weights):
+    """float32 CUDA weight grid(s) as pyastar2d.astar_path takes them -> packed mask bits.
+    Weight errors (min < 1: astar_wrapper.py:35-37) surface in ``raise_status``."""
+    weights = _need_cuda(weights, 'weights', torch.float32)
+    if weights.dim() == 2:
+        weights = weights.unsqueeze(0)
+    n, H, W = weights.shape
+    ctx = get_context(weights.device)
+    bits = torch.empty((n, H, mask_words(W)), dtype=torch.int32, device=weights.device)
+    ctx.check(ctx.lib.axb_pack_weights(ctx.handle, weights.data_ptr(), n, H, W, bits.data_ptr(), _stream()))
+    return bits
+
+
+def make_pairs(entries):
+    """entries: iterable of (mask_idx, src_off, n_src, dst_off, n_dst) -> (numpy struct array with
+    out_off filled back to back, total output elements, total sources)."""
+    entries = list(entries)
+    arr = np.zeros(len(entries), dtype=_lib.PAIR_DTYPE)
+    off = 0
+    tot_src = 0
+    for i, (m, so, ns, do, nd) in enumerate(entries):
+        arr[i] = (m, so, ns, do, nd, 0, off)
+        off += int(ns) * int(nd)
+        tot_src += int(ns)
+    return arr, off, tot_src
+
+
+def cost_matrix_batch(mask_bits, W, dets_yx, pairs, max_px=500, want_cost=True, out=None, pairs_dev=None):
+    """Path-length cost matrices of many frame pairs in one launch.
+
+    mask_bits int32 CUDA [n_masks, H, Wp] from pack_mask; dets_yx int32 CUDA [n, 2] rows (y, x);
+    pairs = numpy struct array from make_pairs (or the entries themselves).
+    Returns (path_len int32 flat, unreachable uint8 flat, wcost float32 flat | None, pairs);
+    pair p's block is [out_off : out_off + n_src*n_dst] reshaped [n_src, n_dst].
+    Replaces AxonDetections._compute_detections_astar_paths + _get_astar_path_distances
+    (AxonDetections.py:526-585, 717-752)."""
+    mask_bits = _need_cuda(mask_bits, 'mask_bits', torch.int32)
+    dets_yx = _need_cuda(dets_yx, 'dets_yx', torch.int32)
+    if not isinstance(pairs, np.ndarray):
+        pairs, _, _ = make_pairs(pairs)
+    n_pairs = len(pairs)
+    total = int((pairs['out_off'] + pairs['n_src'].astype(np.int64) * pairs['n_dst']).max()) if n_pairs else 0
+    total_src = int(pairs['n_src'].sum()) if n_pairs else 0
+    dev = mask_bits.device
+    ctx = get_context(dev)
+    if out is None:
+        path_len = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+        unreach = torch.empty(max(total, 1), dtype=torch.uint8, device=dev)
+        wcost = torch.empty(max(total, 1), dtype=torch.float32, device=dev) if want_cost else None
+    else:
+        path_len, unreach, wcost = out
+    if n_pairs and total:
+        if pairs_dev is None:
+            pairs_dev = torch.from_numpy(pairs.view(np.uint8).reshape(-1).copy()).to(dev, non_blocking=False)
+        n_masks, H, _ = mask_bits.shape
+        ctx.check(ctx.lib.axb_cost_matrix_batch(
+            ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), dets_yx.data_ptr(),
+            pairs_dev.data_ptr(), n_pairs, total_src, int(max_px),
+            path_len.data_ptr(), unreach.data_ptr(), wcost.data_ptr() if wcost is not None else None,
+            _stream()))
+    return path_len[:total], unreach[:total], (wcost[:total] if wcost is not None else None), pairs
+
+
+def cost_matrix(mask_bits, W, src_yx, dst_yx, max_px=500, want_cost=True):
+    """One frame pair: -> (path_len [n_src,n_dst] int32, unreachable uint8, wcost float32|None)."""
+    mask_bits = _need_cuda(mask_bits, 'mask_bits', torch.int32)
+    if mask_bits.dim() == 3:
+        assert mask_bits.shape[0] == 1
+        mask_bits = mask_bits[0]
+    src_yx = _need_cuda(src_yx, 'src_yx', torch.int32).reshape(-1, 2)
+    dst_yx = _need_cuda(dst_yx, 'dst_yx', torch.int32).reshape(-1, 2)
+    ns, nd = src_yx.shape[0], dst_yx.shape[0]
+    dev = mask_bits.device
+    ctx = get_context(dev)
+    path_len = torch.empty((ns, nd), dtype=torch.int32, device=dev)
+    unreach = torch.empty((ns, nd), dtype=torch.uint8, device=dev)
+    wcost = torch.empty((ns, nd), dtype=torch.float32, device=dev) if want_cost else None
+    if ns and nd:
+        ctx.check(ctx.lib.axb_cost_matrix(
+            ctx.handle, mask_bits.data_ptr(), mask_bits.shape[0], int(W), src_yx.data_ptr(), ns,
+            dst_yx.data_ptr(), nd, int(max_px), path_len.data_ptr(), unreach.data_ptr(),
+            wcost.data_ptr() if wcost is not None else None, _stream()))
+    return path_len, unreach, wcost
+
+
+def decode_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23, cap=None, want_pre=True):
+    """Fused decode + threshold + stitch + NMS of F frames.
+
+    Y float32 CUDA [F, ntiles, Sx, Sy, 3]; tile_yx int32 CUDA [ntiles, 2].
+    Returns dict of CUDA tensors: n_pre [F], pre_conf [F,cap], pre_xy [F,cap,2] (x, y),
+    pre_tile [F,cap], n_out [F], conf [F,cap], xy [F,cap,2] (x, y), keep_idx [F,cap].
+    Replaces _yolo_Y2pandas_det + stitch_tiles + _non_max_supression
+    (AxonDetections.py:178-278, Timelapse.py:166-197)."""
+    Y = _need_cuda(Y, 'Y', torch.float32)
+    if Y.dim() == 4:
+        Y = Y.unsqueeze(0)
+    tile_yx = _need_cuda(tile_yx, 'tile_yx', torch.int32)
+    F, ntiles, Sx, Sy, C = Y.shape
+    assert C == 3 and tile_yx.shape == (ntiles, 2)
+    if cap is None:
+        cap = ntiles * Sx * Sy
+    dev = Y.device
+    ctx = get_context(dev)
+    o = dict(n_pre=torch.zeros(F, dtype=torch.int32, device=dev),
+             n_out=torch.zeros(F, dtype=torch.int32, device=dev),
+             conf=torch.empty((F, cap), dtype=torch.float32, device=dev),
+             xy=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
+             keep_idx=torch.empty((F, cap), dtype=torch.int32, device=dev))
+    if want_pre:
+        o.update(pre_conf=torch.empty((F, cap), dtype=torch.float32, device=dev),
+                 pre_xy=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
+                 pre_tile=torch.empty((F, cap), dtype=torch.int32, device=dev))
+    ptr = lambda k: o[k].data_ptr() if k in o else None
+    ctx.check(ctx.lib.axb_decode_nms(
+        ctx.handle, Y.data_ptr(), tile_yx.data_ptr(), F, ntiles, Sx, Sy, int(tilesize),
+        ctypes.c_float(float(np.float32(conf_thr))), int(nms_dist), int(cap),
+        ptr('pre_conf'), ptr('pre_xy'), ptr('pre_tile'), o['n_pre'].data_ptr(),
+        o['conf'].data_ptr(), o['xy'].data_ptr(), o['keep_idx'].data_ptr(), o['n_out'].data_ptr(),
+        _stream()))
+    return o
+
+
+def raise_status(pairs=None, dets_yx_host=None, device=None):
+    """Synchronise and raise the reference's exception for the first input error, if any
+    (astar_wrapper.py:35-45: ValueError for weights < 1, out-of-grid start / goal)."""
+    ctx = get_context(device)
+    rc, (p, i, j) = ctx.status(_stream())
+    if rc == _lib.OK:
+        return
+    if rc == _lib.ERR_BAD_WEIGHT:
+        raise ValueError('Minimum cost to move must be 1, but got a smaller weight')
+    if rc in (_lib.ERR_OOB_START, _lib.ERR_OOB_GOAL) and pairs is not None and dets_yx_host is not None and p >= 0:
+        d = np.asarray(dets_yx_host).reshape(-1, 2)
+        if rc == _lib.ERR_OOB_START:
+            y, x = d[int(pairs['src_off'][p]) + i]
+            raise ValueError(f'Start of {(int(y), int(x))} lies outside grid.')
+        y, x = d[int(pairs['dst_off'][p]) + j]
+        raise ValueError(f'Goal of {(int(y), int(x))} lies outside grid.')
+    if rc == _lib.ERR_OOB_START:
+        raise ValueError('Start lies outside grid.')
+    if rc == _lib.ERR_OOB_GOAL:
+        raise ValueError('Goal lies outside grid.')
+    raise _lib.AxbError(rc, 'device-side status')

@@ -1,0 +1,160 @@
+/* axtrack_b200 -- C ABI of the B200-native AxTrack association hot path.
+ *
+ * This is the drop-in boundary: a plain C shared library (libaxtrack_b200.so), no torch or
+ * Python types in any signature.  Every entry point names the reference interface it replaces
+ * (paths relative to the reference checkout, LoaloaF/axtrack @ 47bfa98).
+ *
+ * Conventions
+ *   - all `*_dev` pointers are CUDA device pointers owned by the caller (e.g. torch tensors);
+ *     `*_host` pointers are host memory (pinned for best speed); nothing is allocated for the
+ *     caller and nothing is kept after the call returns except ctx-owned scratch;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream); device
+ *     entry points are asynchronous on that stream; one ctx may be used from one thread at a
+ *     time (create one ctx per thread / per stream for concurrency);
+ *   - return value: AXB_OK or a negative AXB_ERR_* code.  Input errors that the reference
+ *     raises from inside pyastar2d (out-of-grid start / goal, astar_wrapper.py:39-45) are
+ *     detected on the device and reported by axb_status() after the stream has drained;
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     AXB_ERR_CUDA.
+ */
+#ifndef AXTRACK_B200_H
+#define AXTRACK_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AXB_OK                 0
+#define AXB_ERR_CUDA          -1   /* CUDA runtime error / no device; see axb_last_error()      */
+#define AXB_ERR_OOB_START     -2   /* "Start of (y, x) lies outside grid."  astar_wrapper.py:39-42 */
+#define AXB_ERR_OOB_GOAL      -3   /* "Goal of (y, x) lies outside grid."   astar_wrapper.py:43-45 */
+#define AXB_ERR_BAD_WEIGHT    -4   /* "Minimum cost to move must be 1"      astar_wrapper.py:35-37 */
+#define AXB_ERR_BAD_ARG       -5   /* NULL pointer, negative size, max_px outside [1, AXB_MAX_PX] */
+#define AXB_ERR_CAPACITY      -6   /* more detections than `cap` in axb_decode_nms              */
+#define AXB_ERR_UNSUPPORTED_WEIGHT -7 /* weight grid holds values other than {1, 65536}        */
+
+/* Largest max_px (the reference's max_px_assoc_dist / max_path_length; 500 in
+ * AxonDetections.py:77) the shared-memory search window supports. */
+#define AXB_MAX_PX 511
+
+typedef struct axb_ctx axb_ctx;
+
+/* One frame pair = one key f'{name}_t:{t:0>3}-t:{t_bef:0>3}' of astar_dets_paths
+ * (AxonDetections.py:563).  Sources are the detections of the predecessor frame t_bef,
+ * targets those of frame t, the mask is frame t's (AxonDetections.py:556-566). */
+typedef struct axb_pair_desc {
+    int32_t mask_idx;   /* which packed mask of `mask_bits_dev` (frame t's)                    */
+    int32_t src_off;    /* first source detection in dets_yx_dev (rows of (y, x))             */
+    int32_t n_src;      /* n_pred                                                              */
+    int32_t dst_off;    /* first target detection in dets_yx_dev                              */
+    int32_t n_dst;      /* n_cur                                                               */
+    int32_t reserved;
+    int64_t out_off;    /* element offset of this pair's [n_src, n_dst] block in the outputs  */
+} axb_pair_desc;
+
+/* ---- lifetime ------------------------------------------------------------------------- */
+int  axb_create(int device, axb_ctx** out);
+void axb_destroy(axb_ctx* ctx);
+const char* axb_last_error(const axb_ctx* ctx);
+const char* axb_version(void);
+/* number of kernels this ctx has launched since creation (bench.py's gpu_launches) */
+int64_t axb_launch_count(const axb_ctx* ctx);
+
+/* ---- mask ------------------------------------------------------------------------------
+ * Replaces AxonDetections._get_maskweights (AxonDetections.py:587-598), which expands the
+ * boolean mask to float32 weights where(mask==1, 1, 65536).  Here the mask is bit-packed
+ * once per frame: bit (x & 31) of word [y][x >> 5] = (mask[y][x] == 1).
+ * axb_mask_words(W) = words per packed row. */
+int axb_mask_words(int W);
+int axb_pack_mask(axb_ctx* ctx, const uint8_t* mask_dev, int n_masks, int H, int W,
+                  uint32_t* mask_bits_dev, void* stream);
+/* Same from a float32 weight grid as pyastar2d.astar_path receives it
+ * (astar_wrapper.py:25-37).  Sets the sticky status AXB_ERR_BAD_WEIGHT if any weight < 1 and
+ * AXB_ERR_UNSUPPORTED_WEIGHT if any weight is neither 1 nor 65536. */
+int axb_pack_weights(axb_ctx* ctx, const float* weights_dev, int n_masks, int H, int W,
+                     uint32_t* mask_bits_dev, void* stream);
+
+/* ---- A* path-length cost matrix --------------------------------------------------------
+ * Replaces, for all (source, target) pairs of the given frame pairs, the reference's
+ *   AxonDetections._compute_detections_astar_paths     AxonDetections.py:526-585
+ *     -> _get_path_between_dets                        AxonDetections.py:600-629
+ *     -> utils._compute_astar_path                     utils.py:351-390
+ *     -> pyastar2d.astar_path / astar()                astar_wrapper.py:25-54, astar.cpp:46-172
+ *   followed by _get_astar_path_distances              AxonDetections.py:717-752
+ * Outputs, for pair p, source i, target j at element out_off + i*n_dst + j:
+ *   path_len    int32  number of pixels on the A* path (both ends included), or max_px when the
+ *               reference leaf is None (AxonDetections.py:736)
+ *   unreachable uint8  1 where the reference leaf is None (Euclid distance >= max_px, or the
+ *               search hit the max_path_length cut-off, astar.cpp:88-92), else 0
+ *   wcost       float32 (optional, may be NULL) cost of the returned path = sum of weights over
+ *               path[1:] (astar.cpp:122), +inf where unreachable
+ * dets_yx_dev: int32 [n, 2] rows (y, x).  pairs_dev: n_pairs descriptors in DEVICE memory.
+ * total_src = sum of n_src over the pairs (host value, sizes the work list). */
+int axb_cost_matrix_batch(axb_ctx* ctx,
+                          const uint32_t* mask_bits_dev, int n_masks, int H, int W,
+                          const int32_t* dets_yx_dev,
+                          const axb_pair_desc* pairs_dev, int n_pairs, int total_src,
+                          int max_px,
+                          int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev,
+                          void* stream);
+
+/* Single frame pair, device buffers (a 1-element batch). */
+int axb_cost_matrix(axb_ctx* ctx, const uint32_t* mask_bits_dev, int H, int W,
+                    const int32_t* src_yx_dev, int n_src, const int32_t* dst_yx_dev, int n_dst,
+                    int max_px,
+                    int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev,
+                    void* stream);
+
+/* Many frame pairs, HOST buffers: uint8 masks [n_masks, H, W], host detections [n_dets, 2],
+ * host descriptors, host outputs; does the host->device copies, the mask packing, the search
+ * and the device->host copies on the ctx's own stream and synchronises.  This is the call a
+ * non-torch binding of _compute_detections_astar_paths (AxonDetections.py:526-585) makes, and
+ * what bench.py times as `e2e`. */
+int axb_cost_matrix_batch_host(axb_ctx* ctx, const uint8_t* masks_host, int n_masks, int H, int W,
+                               const int32_t* dets_yx_host, int n_dets,
+                               const axb_pair_desc* pairs_host, int n_pairs, int max_px,
+                               int32_t* path_len_host, uint8_t* unreachable_host, float* wcost_host);
+
+/* Single frame pair, HOST buffers: uint8 mask [H, W], host detections, host outputs; does the
+ * host<->device copies and synchronises (a 1-element axb_cost_matrix_batch_host). */
+int axb_cost_matrix_host(axb_ctx* ctx, const uint8_t* mask_host, int H, int W,
+                         const int32_t* src_yx_host, int n_src,
+                         const int32_t* dst_yx_host, int n_dst, int max_px,
+                         int32_t* path_len_host, uint8_t* unreachable_host, float* wcost_host);
+
+/* ---- decode + confidence threshold + NMS ------------------------------------------------
+ * Replaces, per frame,
+ *   AxonDetections._yolo_Y2pandas_det       AxonDetections.py:178-248
+ *   Timelapse.stitch_tiles (coordinates)    Timelapse.py:166-197 (+ :141-148)
+ *   AxonDetections._non_max_supression      AxonDetections.py:250-278
+ * Y_dev      float32 [F, ntiles, Sx, Sy, 3] detector output (conf, x, y) per grid cell
+ *            (model.py:119-125); dim 1 of a tile is the x cell, dim 2 the y cell
+ * tile_yx_dev int32 [ntiles, 2] (tile_y, tile_x) of each compact tile (Timelapse.py:141-148)
+ * Outputs (cap = row pitch; AXB_ERR_CAPACITY is set if a frame has more candidates):
+ *   pre_*     the stitched pre-NMS frame detections in the reference's concat order
+ *             (tile-major; inside a tile conf ascending): conf, (x, y) frame coords, tile index
+ *   n_pre     int32 [F]
+ *   conf/xy   NMS survivors in conf-descending order; keep_idx = their pre-NMS indices
+ *   n_out     int32 [F]
+ * Any of the pre_* pointers may be NULL. */
+int axb_decode_nms(axb_ctx* ctx, const float* Y_dev, const int32_t* tile_yx_dev,
+                   int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist,
+                   int cap,
+                   float* pre_conf_dev, int32_t* pre_xy_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
+                   float* conf_dev, int32_t* xy_dev, int32_t* keep_idx_dev, int32_t* n_out_dev,
+                   void* stream);
+
+/* ---- status ----------------------------------------------------------------------------
+ * Synchronises `stream` and returns the sticky device-side status of the calls issued on this
+ * ctx since the last axb_status(): AXB_OK, or the FIRST error in the reference's iteration
+ * order (pairs in the order given, sources ascending, targets ascending;
+ * AxonDetections.py:553-576).  For AXB_ERR_OOB_*: info[0] = pair index, info[1] = source
+ * index, info[2] = target index.  The status is cleared. */
+int axb_status(axb_ctx* ctx, void* stream, int64_t info[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AXTRACK_B200_H */

@@ -1,0 +1,293 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the AxTrack association hot path.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this package, and only as the checker or as the timed
+CPU baseline.  The product (``axtrack_b200``) never imports it.
+
+Contents
+--------
+* ctypes bindings of ``oracle/liboracle.so`` (``astar_oracle.cpp``): the forked pyastar2d
+  search restated (``astar_weights``, ``astar_mask``), the reference's pair loop
+  (``cost_matrix_astar``) and the closed form the CUDA kernel implements (``cost_matrix_rule``).
+* ``ref_astar_path`` / ``ref_cost_matrix``: the reference's OWN compiled pyastar2d fork
+  (``oracle/_ref/astar*.so``, built by ``oracle/Makefile`` from
+  /root/reference/pyastar2d/src/cpp/astar.cpp) driven the way the reference drives it
+  (astar_wrapper.py:25-54, AxonDetections.py:553-579,600-629).
+* ``decode_stitch_nms``: numpy restatement of ``_yolo_Y2pandas_det`` + ``stitch_tiles`` +
+  ``_non_max_supression`` (AxonDetections.py:178-278, Timelapse.py:141-148,166-197).
+* ``transition_cost``: ``transition_model`` with ``vis_sim_weight`` handled as in the
+  reference (mincostflow_models.py:67-119) for the deployed ``MCF_VIS_SIM_WEIGHT = 0``.
+
+Parity status: pinned (tests/test_oracle_golden.py, tests/golden/).
+"""
+import ctypes
+import importlib.machinery
+import importlib.util
+import glob
+import os
+import subprocess
+from concurrent.futures import ThreadPoolExecutor
+from itertools import repeat
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_REF = None
+
+ERR_OOB_START = -2
+ERR_OOB_GOAL = -3
+
+
+def build(force=False):
+    """Compile liboracle.so (and oracle/_ref when /root/reference is present)."""
+    so = os.path.join(_HERE, 'liboracle.so')
+    src = os.path.join(_HERE, 'astar_oracle.cpp')
+    need = force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src)
+    have_ref = bool(glob.glob(os.path.join(_HERE, '_ref', 'astar*.so')))
+    if need or (not have_ref and os.path.exists('/root/reference/pyastar2d/src/cpp/astar.cpp')):
+        subprocess.run(['make', '-C', _HERE, '-B' if force else '-s'], check=True,
+                       stdout=subprocess.DEVNULL)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        build()
+        L = ctypes.CDLL(os.path.join(_HERE, 'liboracle.so'))
+        i32p = np.ctypeslib.ndpointer(np.int32, flags='C_CONTIGUOUS')
+        u8p = np.ctypeslib.ndpointer(np.uint8, flags='C_CONTIGUOUS')
+        f32p = np.ctypeslib.ndpointer(np.float32, flags='C_CONTIGUOUS')
+        c_int = ctypes.c_int
+        L.axo_astar_weights.restype = c_int
+        L.axo_astar_weights.argtypes = [f32p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                        ctypes.POINTER(ctypes.c_float), ctypes.c_void_p]
+        L.axo_astar_mask.restype = c_int
+        L.axo_astar_mask.argtypes = [u8p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                     ctypes.POINTER(ctypes.c_float)]
+        for fn in (L.axo_cost_matrix_astar, L.axo_cost_matrix_rule):
+            fn.restype = c_int
+            fn.argtypes = [u8p, c_int, c_int, i32p, c_int, i32p, c_int, c_int,
+                           i32p, u8p, f32p, ctypes.POINTER(ctypes.c_int64)]
+        _LIB = L
+    return _LIB
+
+
+# ----------------------------------------------------------------------------------------
+# restated search
+# ----------------------------------------------------------------------------------------
+def astar_weights(weights, start, goal, max_path_length=10000, return_cost=False):
+    """Forked pyastar2d.astar_path restated (astar_wrapper.py:25-54 + astar.cpp:46-172).
+
+    Returns int32 [L,2] (row, col) or None, raising the wrapper's errors."""
+    assert weights.dtype == np.float32, (
+        f"weights must have np.float32 data type, but has {weights.dtype}")
+    if weights.min(axis=None) < 1.:
+        raise ValueError("Minimum cost to move must be 1, but got %f" % (weights.min(axis=None)))
+    H, W = weights.shape
+    if start[0] < 0 or start[0] >= H or start[1] < 0 or start[1] >= W:
+        raise ValueError(f"Start of {start} lies outside grid.")
+    if goal[0] < 0 or goal[0] >= H or goal[1] < 0 or goal[1] >= W:
+        raise ValueError(f"Goal of {goal} lies outside grid.")
+    w = np.ascontiguousarray(weights)
+    cap = int(min(max_path_length, H * W))
+    path = np.empty((max(cap, 1), 2), np.int32)
+    cost = ctypes.c_float(0)
+    L = lib().axo_astar_weights(w.reshape(-1), H, W, int(start[0]), int(start[1]), int(goal[0]),
+                                int(goal[1]), int(max_path_length), ctypes.byref(cost),
+                                path.ctypes.data_as(ctypes.c_void_p))
+    if L < 0:
+        return (None, None) if return_cost else None
+    return (path[:L].copy(), cost.value) if return_cost else path[:L].copy()
+
+
+def _prep(mask, src_yx, dst_yx):
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    src = np.ascontiguousarray(np.asarray(src_yx, dtype=np.int32).reshape(-1, 2))
+    dst = np.ascontiguousarray(np.asarray(dst_yx, dtype=np.int32).reshape(-1, 2))
+    n = max(src.shape[0] * dst.shape[0], 1)
+    return mask, src, dst, np.empty(n, np.int32), np.empty(n, np.uint8), np.empty(n, np.float32)
+
+
+def _raise(code, pair, src, dst):
+    i, j = divmod(int(pair), max(dst.shape[0], 1))
+    if code == ERR_OOB_START:
+        raise ValueError(f"Start of {(int(src[i, 0]), int(src[i, 1]))} lies outside grid.")
+    if code == ERR_OOB_GOAL:
+        raise ValueError(f"Goal of {(int(dst[j, 0]), int(dst[j, 1]))} lies outside grid.")
+    raise RuntimeError(f'oracle error {code}')
+
+
+def _cost_matrix(fn, mask, src_yx, dst_yx, max_px):
+    mask, src, dst, pl, un, wc = _prep(mask, src_yx, dst_yx)
+    err = ctypes.c_int64(-1)
+    rc = fn(mask.reshape(-1), mask.shape[0], mask.shape[1], src.reshape(-1), src.shape[0],
+            dst.reshape(-1), dst.shape[0], int(max_px), pl, un, wc, ctypes.byref(err))
+    if rc != 0:
+        _raise(rc, err.value, src, dst)
+    shp = (src.shape[0], dst.shape[0])
+    k = shp[0] * shp[1]
+    return pl[:k].reshape(shp), un[:k].reshape(shp), wc[:k].reshape(shp)
+
+
+def cost_matrix_astar(mask, src_yx, dst_yx, max_px=500):
+    """Per-pair restated A* (the reference's loop).  -> (path_len i32, unreachable u8, wcost f32)."""
+    return _cost_matrix(lib().axo_cost_matrix_astar, mask, src_yx, dst_yx, max_px)
+
+
+def cost_matrix_rule(mask, src_yx, dst_yx, max_px=500):
+    """Closed form (one bounded search per source).  Same outputs as cost_matrix_astar."""
+    return _cost_matrix(lib().axo_cost_matrix_rule, mask, src_yx, dst_yx, max_px)
+
+
+# ----------------------------------------------------------------------------------------
+# the reference's own compiled search (oracle/_ref)
+# ----------------------------------------------------------------------------------------
+def ref_available():
+    return bool(glob.glob(os.path.join(_HERE, '_ref', 'astar*.so')))
+
+
+def ref_module():
+    """Import oracle/_ref/astar*.so -- the reference's CPython extension, unmodified."""
+    global _REF
+    if _REF is None:
+        build()
+        cands = glob.glob(os.path.join(_HERE, '_ref', 'astar*.so'))
+        if not cands:
+            raise ImportError('oracle/_ref/astar*.so not built (needs /root/reference at build time)')
+        loader = importlib.machinery.ExtensionFileLoader('astar', cands[0])
+        spec = importlib.util.spec_from_loader('astar', loader)
+        mod = importlib.util.module_from_spec(spec)
+        loader.exec_module(mod)
+        _REF = mod
+    return _REF
+
+
+def ref_astar_path(weights, start, goal, max_path_length=10000):
+    """What pyastar2d.astar_path does around the compiled call (astar_wrapper.py:31-53):
+    dtype assert, O(H*W) min scan, bounds checks, ravel, O(H*W) flatten copy, native call."""
+    assert weights.dtype == np.float32, (
+        f"weights must have np.float32 data type, but has {weights.dtype}")
+    if weights.min(axis=None) < 1.:
+        raise ValueError("Minimum cost to move must be 1, but got %f" % (weights.min(axis=None)))
+    if (start[0] < 0 or start[0] >= weights.shape[0] or
+            start[1] < 0 or start[1] >= weights.shape[1]):
+        raise ValueError(f"Start of {start} lies outside grid.")
+    if (goal[0] < 0 or goal[0] >= weights.shape[0] or
+            goal[1] < 0 or goal[1] >= weights.shape[1]):
+        raise ValueError(f"Goal of {goal} lies outside grid.")
+    height, width = weights.shape
+    s = int(np.ravel_multi_index(start, (height, width)))
+    g = int(np.ravel_multi_index(goal, (height, width)))
+    return ref_module().astar(weights.flatten(), height, width, s, g, int(max_path_length))
+
+
+def mask_weights(mask):
+    """AxonDetections._get_maskweights (AxonDetections.py:598)."""
+    return np.where(np.asarray(mask) == 1, 1, 2 ** 16).astype(np.float32)
+
+
+def _ref_pair(src, dst, weights, max_px):
+    # _get_path_between_dets (AxonDetections.py:600-629): dets are (conf, x, y)
+    sy, sx = src
+    ty, tx = dst
+    dist = np.sqrt((sy - ty) ** 2 + (sx - tx) ** 2)
+    if dist < max_px:
+        p = ref_astar_path(weights, (int(sy), int(sx)), (int(ty), int(tx)), max_px)
+        return None if p is None else p.shape[0]
+    return None
+
+
+def ref_cost_matrix(mask, src_yx, dst_yx, max_px=500, threads=True):
+    """The reference's source loop with its ThreadPoolExecutor over targets
+    (AxonDetections.py:570-579) on the compiled reference search; leaves mapped as in
+    _get_astar_path_distances (AxonDetections.py:736).  -> (path_len i64, unreachable u8)."""
+    weights = mask_weights(mask)
+    src = np.asarray(src_yx, dtype=np.int64).reshape(-1, 2)
+    dst = np.asarray(dst_yx, dtype=np.int64).reshape(-1, 2)
+    rows = []
+    for s in src:
+        if threads:
+            with ThreadPoolExecutor() as ex:
+                row = list(ex.map(_ref_pair, repeat(s), dst, repeat(weights), repeat(max_px)))
+        else:
+            row = [_ref_pair(s, d, weights, max_px) for d in dst]
+        rows.append(row)
+    pl = np.array([[max_px if v is None else v for v in r] for r in rows], dtype=np.int64).reshape(len(src), len(dst))
+    un = np.array([[v is None for v in r] for r in rows], dtype=np.uint8).reshape(len(src), len(dst))
+    return pl, un
+
+
+# ----------------------------------------------------------------------------------------
+# decode + stitch + NMS
+# ----------------------------------------------------------------------------------------
+def decode_stitch_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23):
+    """numpy restatement of the per-frame detection path.
+
+    Y       float32 [ntiles, Sx, Sy, 3] = (conf, x, y) per grid cell (model.py:119-125)
+    tile_yx int     [ntiles, 2]         = (tile_y, tile_x) of each compact tile
+                                          (Timelapse.flat_tile_idx2yx_tile_idx, Timelapse.py:141-148)
+    Returns dict with
+      pre_conf/pre_x/pre_y  the stitched pre-NMS frame detections in reference order
+                            (tile-major; inside a tile conf ascending; AxonDetections.py:235,
+                            Timelapse.py:191-196)
+      conf/x/y              NMS survivors, conf descending (AxonDetections.py:261-277)
+      keep_idx              their pre-NMS indices ("survivor indices")
+    Ties in conf: cell order inside a tile (stable), and (conf desc, pre-NMS index asc) for
+    NMS -- the reference's pandas quicksort leaves tie order implementation-defined
+    (SURVEY Appendix B.6); generators avoid ties.
+    """
+    Y = np.asarray(Y, dtype=np.float32)
+    ntiles, Sx, Sy, _ = Y.shape
+    ts = np.float32(tilesize)
+    ix = np.arange(Sx, dtype=np.float32).reshape(1, Sx, 1)
+    iy = np.arange(Sy, dtype=np.float32).reshape(1, 1, Sy)
+    noanchor = (Y == 0).all(-1)
+    # separate f32 add, mul, div, round-half-even (AxonDetections.py:203-207)
+    x = np.rint(((Y[..., 1] + ix).astype(np.float32) * ts).astype(np.float32) / np.float32(Sx))
+    y = np.rint(((Y[..., 2] + iy).astype(np.float32) * ts).astype(np.float32) / np.float32(Sy))
+    conf = Y[..., 0].copy()
+    x[noanchor] = 0
+    y[noanchor] = 0
+    conf[noanchor] = 0
+    thr = np.float32(conf_thr)
+    pre_c, pre_x, pre_y = [], [], []
+    for t in range(ntiles):
+        c = conf[t].reshape(-1)
+        keep = np.nonzero(c >= thr)[0]                       # cell order ix*Sy+iy
+        order = keep[np.argsort(c[keep], kind='stable')]      # conf ascending
+        pre_c.append(c[order])
+        pre_x.append(x[t].reshape(-1)[order].astype(np.int64) + int(tile_yx[t][1]) * tilesize)
+        pre_y.append(y[t].reshape(-1)[order].astype(np.int64) + int(tile_yx[t][0]) * tilesize)
+    pre_c = np.concatenate(pre_c) if pre_c else np.zeros(0, np.float32)
+    pre_x = np.concatenate(pre_x) if pre_x else np.zeros(0, np.int64)
+    pre_y = np.concatenate(pre_y) if pre_y else np.zeros(0, np.int64)
+    n = pre_c.shape[0]
+    order = np.argsort(-pre_c.astype(np.float64), kind='stable')   # conf desc, idx asc on ties
+    alive = np.ones(n, bool)
+    keep_idx = []
+    d2max = int(nms_dist) * int(nms_dist)
+    for i in order:
+        if not alive[i]:
+            continue
+        keep_idx.append(i)
+        d2 = (pre_x - pre_x[i]) ** 2 + (pre_y - pre_y[i]) ** 2
+        alive &= ~(d2 < d2max)
+    keep_idx = np.array(keep_idx, dtype=np.int64)
+    return dict(pre_conf=pre_c, pre_x=pre_x, pre_y=pre_y, keep_idx=keep_idx,
+                conf=pre_c[keep_idx], x=pre_x[keep_idx], y=pre_y[keep_idx])
+
+
+# ----------------------------------------------------------------------------------------
+# transition_model (consumer; the "final cost matrix")
+# ----------------------------------------------------------------------------------------
+def transition_cost(path_len, max_px=500, miss_rate=0.6, time_gap=1, vis_sim_weight=0.0, vis_sim=None):
+    """mincostflow_models.py:100-119 for given A* distances (float64)."""
+    distances = ((np.asarray(path_len) / max_px) - 1) * -1
+    inf_dist = distances == 0
+    if vis_sim is None:
+        vis_sim = np.zeros_like(distances)
+    costs = -np.log((1 - vis_sim_weight) * distances * (miss_rate ** (time_gap - 1))
+                    + vis_sim_weight * vis_sim + 1e-6)
+    costs[inf_dist] = np.inf
+    return costs
