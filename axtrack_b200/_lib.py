@@ -24,7 +24,7 @@ MAX_PX = 511
 SYMBOLS = ('axb_create', 'axb_destroy', 'axb_last_error', 'axb_version', 'axb_launch_count',
            'axb_mask_words', 'axb_pack_mask', 'axb_pack_weights', 'axb_cost_matrix_batch',
            'axb_cost_matrix', 'axb_cost_matrix_batch_host', 'axb_cost_matrix_host',
-           'axb_decode_nms', 'axb_status')
+           'axb_decode_nms', 'axb_decode_nms_host', 'axb_status')
 
 
 class PairDesc(ctypes.Structure):
@@ -78,6 +78,9 @@ def load():
     L.axb_decode_nms.restype = ci
     L.axb_decode_nms.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, cf, ci, ci,
                                  vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.axb_decode_nms_host.restype = ci
+    L.axb_decode_nms_host.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, cf, ci, ci,
+                                      vp, vp, vp, vp, vp, vp, vp, vp]
     L.axb_status.restype = ci
     L.axb_status.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_int64 * 3)]
     _lib = L

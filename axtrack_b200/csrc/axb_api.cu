@@ -32,6 +32,8 @@ struct axb_ctx {
     int32_t* st_plen = nullptr;       size_t st_plen_bytes = 0;
     uint8_t* st_unr = nullptr;        size_t st_unr_bytes = 0;
     float* st_wc = nullptr;           size_t st_wc_bytes = 0;
+    // staging for axb_decode_nms_host: one arena
+    uint8_t* st_k1 = nullptr;         size_t st_k1_bytes = 0;
 };
 
 namespace {
@@ -108,7 +110,7 @@ void axb_destroy(axb_ctx* c) {
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_scratch); cudaFree(c->work_counter); cudaFree(c->prefix_dev); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
-    cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc);
+    cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -235,8 +237,19 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
         AXB_CUDA(c, cudaMemcpyAsync(unreachable_host, c->st_unr, (size_t)total_out, cudaMemcpyDeviceToHost, s));
         if (wcost_host) AXB_CUDA(c, cudaMemcpyAsync(wcost_host, c->st_wc, (size_t)total_out * 4, cudaMemcpyDeviceToHost, s));
     }
-    AXB_CUDA(c, cudaStreamSynchronize(s));
-    return AXB_OK;
+    int64_t info[3];
+    rc = axb_status(c, s, info);       // synchronises
+    if ((rc == AXB_ERR_OOB_START || rc == AXB_ERR_OOB_GOAL) && info[0] >= 0 && info[0] < n_pairs) {
+        // the reference's message (astar_wrapper.py:41,45)
+        const axb_pair_desc& pd = pairs_host[info[0]];
+        const bool st = rc == AXB_ERR_OOB_START;
+        const int64_t row = st ? (int64_t)pd.src_off + info[1] : (int64_t)pd.dst_off + info[2];
+        char buf[128];
+        snprintf(buf, sizeof buf, "%s of (%d, %d) lies outside grid.", st ? "Start" : "Goal",
+                 dets_yx_host[2 * row], dets_yx_host[2 * row + 1]);
+        c->err = buf;
+    }
+    return rc;
 }
 
 int axb_cost_matrix_host(axb_ctx* c, const uint8_t* mask_host, int H, int W,
@@ -258,13 +271,13 @@ int axb_cost_matrix_host(axb_ctx* c, const uint8_t* mask_host, int H, int W,
 
 int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
                    int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist, int cap,
-                   float* pre_conf_dev, int32_t* pre_xy_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
-                   float* conf_dev, int32_t* xy_dev, int32_t* keep_idx_dev, int32_t* n_out_dev, void* stream) {
+                   float* pre_conf_dev, int32_t* pre_yx_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
+                   float* conf_dev, int32_t* yx_dev, int32_t* keep_idx_dev, int32_t* n_out_dev, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (F < 0 || ntiles <= 0 || Sx <= 0 || Sy <= 0 || tilesize <= 0 || cap <= 0 || nms_dist < 0 || nms_dist > 30000)
         return bad_arg(c, "axb_decode_nms: bad size");
     if (F == 0) return AXB_OK;
-    if (!Y_dev || !tile_yx_dev || !n_pre_dev || !conf_dev || !xy_dev || !keep_idx_dev || !n_out_dev)
+    if (!Y_dev || !tile_yx_dev || !n_pre_dev || !conf_dev || !yx_dev || !keep_idx_dev || !n_out_dev)
         return bad_arg(c, "axb_decode_nms: NULL pointer");
     const long long ncell_ll = (long long)ntiles * Sx * Sy;
     if (ncell_ll > (1 << 24)) return bad_arg(c, "axb_decode_nms: more than 2^24 grid cells per frame");
@@ -278,13 +291,52 @@ int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
     axb::K1Params p;
     p.Y = Y_dev; p.tile_yx = tile_yx_dev; p.F = F; p.ntiles = ntiles; p.Sx = Sx; p.Sy = Sy; p.tilesize = tilesize;
     p.conf_thr = conf_thr; p.nms_d2 = nms_dist * nms_dist; p.cap = cap;
-    p.pre_conf = pre_conf_dev; p.pre_xy = pre_xy_dev; p.pre_tile = pre_tile_dev; p.n_pre = n_pre_dev;
-    p.conf = conf_dev; p.xy = xy_dev; p.keep_idx = keep_idx_dev; p.n_out = n_out_dev;
+    p.pre_conf = pre_conf_dev; p.pre_yx = pre_yx_dev; p.pre_tile = pre_tile_dev; p.n_pre = n_pre_dev;
+    p.conf = conf_dev; p.yx = yx_dev; p.keep_idx = keep_idx_dev; p.n_out = n_out_dev;
     p.scratch = c->k1_scratch; p.scratch_per_frame = per_frame; p.npad = npad; p.err_flags = c->status_dev + 1;
     axb::launch_k1(p, (cudaStream_t)stream);
     c->launches += 1;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;
+}
+
+int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_host,
+                        int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist, int cap,
+                        float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_tile_host, int32_t* n_pre_host,
+                        float* conf_host, int32_t* yx_host, int32_t* keep_idx_host, int32_t* n_out_host) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (F < 0 || ntiles <= 0 || Sx <= 0 || Sy <= 0 || cap <= 0) return bad_arg(c, "axb_decode_nms_host: bad size");
+    if (F == 0) return AXB_OK;
+    if (!Y_host || !tile_yx_host || !n_pre_host || !conf_host || !yx_host || !keep_idx_host || !n_out_host)
+        return bad_arg(c, "axb_decode_nms_host: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = c->own_stream;
+    auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t nY = (size_t)F * ntiles * Sx * Sy * 3 * 4, nT = (size_t)ntiles * 8, nFC = (size_t)F * cap * 4, nF = (size_t)F * 4;
+    const size_t total = al(nY) + al(nT) + 2 * al(nF) + 3 * al(nFC) + 2 * al(2 * nFC) + al(nFC);
+    int rc = grow(c, &c->st_k1, &c->st_k1_bytes, total);
+    if (rc != AXB_OK) return rc;
+    uint8_t* b = c->st_k1;
+    auto take = [&](size_t bytes) { uint8_t* p = b; b += al(bytes); return p; };
+    float* dY = (float*)take(nY);            int32_t* dT = (int32_t*)take(nT);
+    int32_t* d_npre = (int32_t*)take(nF);    int32_t* d_nout = (int32_t*)take(nF);
+    float* d_pconf = (float*)take(nFC);      int32_t* d_ptile = (int32_t*)take(nFC);    int32_t* d_pyx = (int32_t*)take(2 * nFC);
+    float* d_conf = (float*)take(nFC);       int32_t* d_yx = (int32_t*)take(2 * nFC);   int32_t* d_keep = (int32_t*)take(nFC);
+    AXB_CUDA(c, cudaMemcpyAsync(dY, Y_host, nY, cudaMemcpyHostToDevice, s));
+    AXB_CUDA(c, cudaMemcpyAsync(dT, tile_yx_host, nT, cudaMemcpyHostToDevice, s));
+    rc = axb_decode_nms(c, dY, dT, F, ntiles, Sx, Sy, tilesize, conf_thr, nms_dist, cap,
+                        pre_conf_host ? d_pconf : nullptr, pre_yx_host ? d_pyx : nullptr, pre_tile_host ? d_ptile : nullptr,
+                        d_npre, d_conf, d_yx, d_keep, d_nout, s);
+    if (rc != AXB_OK) return rc;
+    AXB_CUDA(c, cudaMemcpyAsync(n_pre_host, d_npre, nF, cudaMemcpyDeviceToHost, s));
+    AXB_CUDA(c, cudaMemcpyAsync(n_out_host, d_nout, nF, cudaMemcpyDeviceToHost, s));
+    AXB_CUDA(c, cudaMemcpyAsync(conf_host, d_conf, nFC, cudaMemcpyDeviceToHost, s));
+    AXB_CUDA(c, cudaMemcpyAsync(yx_host, d_yx, 2 * nFC, cudaMemcpyDeviceToHost, s));
+    AXB_CUDA(c, cudaMemcpyAsync(keep_idx_host, d_keep, nFC, cudaMemcpyDeviceToHost, s));
+    if (pre_conf_host) AXB_CUDA(c, cudaMemcpyAsync(pre_conf_host, d_pconf, nFC, cudaMemcpyDeviceToHost, s));
+    if (pre_yx_host) AXB_CUDA(c, cudaMemcpyAsync(pre_yx_host, d_pyx, 2 * nFC, cudaMemcpyDeviceToHost, s));
+    if (pre_tile_host) AXB_CUDA(c, cudaMemcpyAsync(pre_tile_host, d_ptile, nFC, cudaMemcpyDeviceToHost, s));
+    return axb_status(c, s, nullptr);
 }
 
 int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {

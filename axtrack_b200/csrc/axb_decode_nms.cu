@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(NT) k1_decode_nms_kernel(const K1Params p) {
         w.p_conf[pi] = conf; w.p_x[pi] = fx; w.p_y[pi] = fy; w.p_tile[pi] = tile;
         w.key[pi] = ((unsigned long long)ordered_bits(conf) << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)pi);
         if (p.pre_conf) p.pre_conf[(size_t)f * p.cap + pi] = conf;
-        if (p.pre_xy) { p.pre_xy[((size_t)f * p.cap + pi) * 2] = fx; p.pre_xy[((size_t)f * p.cap + pi) * 2 + 1] = fy; }
+        if (p.pre_yx) { p.pre_yx[((size_t)f * p.cap + pi) * 2] = fy; p.pre_yx[((size_t)f * p.cap + pi) * 2 + 1] = fx; }
         if (p.pre_tile) p.pre_tile[(size_t)f * p.cap + pi] = tile;
     }
     int nsort = 1;
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(NT) k1_decode_nms_kernel(const K1Params p) {
             const int pi = w.s_p[r];
             const size_t o = (size_t)f * p.cap + slot;
             p.conf[o] = w.p_conf[pi];
-            p.xy[2 * o] = w.s_x[r]; p.xy[2 * o + 1] = w.s_y[r];
+            p.yx[2 * o] = w.s_y[r]; p.yx[2 * o + 1] = w.s_x[r];
             p.keep_idx[o] = pi;
         }
     }

@@ -9,6 +9,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from .ops_pairs import make_pairs  # noqa: F401  (re-exported)
 
 _contexts = {}
 
@@ -68,20 +69,6 @@ def pack_weights(weights):
     bits = torch.empty((n, H, mask_words(W)), dtype=torch.int32, device=weights.device)
     ctx.check(ctx.lib.axb_pack_weights(ctx.handle, weights.data_ptr(), n, H, W, bits.data_ptr(), _stream()))
     return bits
-
-
-def make_pairs(entries):
-    """entries: iterable of (mask_idx, src_off, n_src, dst_off, n_dst) -> (numpy struct array with
-    out_off filled back to back, total output elements, total sources)."""
-    entries = list(entries)
-    arr = np.zeros(len(entries), dtype=_lib.PAIR_DTYPE)
-    off = 0
-    tot_src = 0
-    for i, (m, so, ns, do, nd) in enumerate(entries):
-        arr[i] = (m, so, ns, do, nd, 0, off)
-        off += int(ns) * int(nd)
-        tot_src += int(ns)
-    return arr, off, tot_src
 
 
 def cost_matrix_batch(mask_bits, W, dets_yx, pairs, max_px=500, want_cost=True, out=None, pairs_dev=None):
@@ -146,8 +133,8 @@ def decode_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23, cap=None, w
     """Fused decode + threshold + stitch + NMS of F frames.
 
     Y float32 CUDA [F, ntiles, Sx, Sy, 3]; tile_yx int32 CUDA [ntiles, 2].
-    Returns dict of CUDA tensors: n_pre [F], pre_conf [F,cap], pre_xy [F,cap,2] (x, y),
-    pre_tile [F,cap], n_out [F], conf [F,cap], xy [F,cap,2] (x, y), keep_idx [F,cap].
+    Returns dict of CUDA tensors: n_pre [F], pre_conf [F,cap], pre_yx [F,cap,2] (y, x),
+    pre_tile [F,cap], n_out [F], conf [F,cap], yx [F,cap,2] (y, x), keep_idx [F,cap].
     Replaces _yolo_Y2pandas_det + stitch_tiles + _non_max_supression
     (AxonDetections.py:178-278, Timelapse.py:166-197)."""
     Y = _need_cuda(Y, 'Y', torch.float32)
@@ -163,18 +150,18 @@ def decode_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23, cap=None, w
     o = dict(n_pre=torch.zeros(F, dtype=torch.int32, device=dev),
              n_out=torch.zeros(F, dtype=torch.int32, device=dev),
              conf=torch.empty((F, cap), dtype=torch.float32, device=dev),
-             xy=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
+             yx=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
              keep_idx=torch.empty((F, cap), dtype=torch.int32, device=dev))
     if want_pre:
         o.update(pre_conf=torch.empty((F, cap), dtype=torch.float32, device=dev),
-                 pre_xy=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
+                 pre_yx=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
                  pre_tile=torch.empty((F, cap), dtype=torch.int32, device=dev))
     ptr = lambda k: o[k].data_ptr() if k in o else None
     ctx.check(ctx.lib.axb_decode_nms(
         ctx.handle, Y.data_ptr(), tile_yx.data_ptr(), F, ntiles, Sx, Sy, int(tilesize),
         ctypes.c_float(float(np.float32(conf_thr))), int(nms_dist), int(cap),
-        ptr('pre_conf'), ptr('pre_xy'), ptr('pre_tile'), o['n_pre'].data_ptr(),
-        o['conf'].data_ptr(), o['xy'].data_ptr(), o['keep_idx'].data_ptr(), o['n_out'].data_ptr(),
+        ptr('pre_conf'), ptr('pre_yx'), ptr('pre_tile'), o['n_pre'].data_ptr(),
+        o['conf'].data_ptr(), o['yx'].data_ptr(), o['keep_idx'].data_ptr(), o['n_out'].data_ptr(),
         _stream()))
     return o
 

@@ -1,0 +1,92 @@
+"""The association hot path of a whole timelapse on one GPU, device resident.
+
+``associate_frames`` = what AxonDetections.detect_dataset's loop body does after the model
+forward (decode + stitch + NMS, /root/reference/axtrack/AxonDetections.py:122-128) for ALL frames
+in one launch, followed by AxonDetections._compute_detections_astar_paths +
+_get_astar_path_distances (AxonDetections.py:526-585, 717-752) for ALL (t, t_bef) keys in one
+launch.  PyTorch only owns the buffers and the stream.
+"""
+import numpy as np
+import torch
+
+from . import _lib, ops
+
+
+def frame_pair_keys(T, max_num_misses=1, t0=0):
+    """[(t, t_bef)] in the reference's loop order (AxonDetections.py:553-566):
+    for t: for t_bef in t-1 .. t-(max_num_misses+1), skipping t_bef < 0."""
+    keys = []
+    for t in range(t0, T):
+        for tb in range(t - 1, t - (max_num_misses + 2), -1):
+            if tb >= 0:
+                keys.append((t, tb))
+    return keys
+
+
+def build_pairs(n_out, cap, keys, mask_of_frame=None):
+    """Pair descriptors for detections stored as [F, cap, 2]: frame f's rows start at f*cap."""
+    entries = []
+    for t, tb in keys:
+        m = 0 if mask_of_frame is None else int(mask_of_frame[t])
+        entries.append((m, tb * cap, int(n_out[tb]), t * cap, int(n_out[t])))
+    return ops.make_pairs(entries)
+
+
+class Association:
+    """Device-resident result of ``associate_frames``."""
+
+    def __init__(self, det, n_out, keys, pairs, path_len, unreachable, wcost, launches):
+        self.det = det                # dict of CUDA tensors from ops.decode_nms
+        self.n_out = n_out            # numpy int32 [T]
+        self.keys = keys              # [(t, t_bef)]
+        self.pairs = pairs            # numpy struct array (axb_pair_desc)
+        self.path_len = path_len      # CUDA int32 flat
+        self.unreachable = unreachable
+        self.wcost = wcost
+        self.launches = launches
+        self._host = None
+
+    def frame_dets(self, t):
+        """numpy: conf (desc), x, y, keep_idx of frame t's NMS survivors."""
+        n = int(self.n_out[t])
+        yx = self.det['yx'][t, :n].cpu().numpy()
+        return dict(conf=self.det['conf'][t, :n].cpu().numpy(), x=yx[:, 1].astype(np.int64),
+                    y=yx[:, 0].astype(np.int64), keep_idx=self.det['keep_idx'][t, :n].cpu().numpy().astype(np.int64))
+
+    def pair_matrices(self):
+        """{(t, t_bef): (path_len [n_pred,n_cur] int32, unreachable uint8, wcost float32|None)} on the host."""
+        if self._host is None:
+            pl = self.path_len.cpu().numpy()
+            un = self.unreachable.cpu().numpy()
+            wc = self.wcost.cpu().numpy() if self.wcost is not None else None
+            out = {}
+            for k, pd in zip(self.keys, self.pairs):
+                o, ns, nd = int(pd['out_off']), int(pd['n_src']), int(pd['n_dst'])
+                sl = slice(o, o + ns * nd)
+                out[k] = (pl[sl].reshape(ns, nd), un[sl].reshape(ns, nd),
+                          wc[sl].reshape(ns, nd) if wc is not None else None)
+            self._host = out
+        return self._host
+
+
+def associate_frames(Y, tile_yx, mask, max_px=500, max_num_misses=1, tilesize=512, conf_thr=0.55,
+                     nms_dist=23, cap=None, mask_of_frame=None, want_cost=True, want_pre=False,
+                     mask_bits=None, t0=0):
+    """Y float32 CUDA [T, ntiles, Sx, Sy, 3]; tile_yx int32 CUDA [ntiles, 2]; mask uint8/bool CUDA
+    [H, W] (static, the reference stacks one 2-D mask: Timelapse.py:213-214) or [n_masks, H, W] with
+    ``mask_of_frame`` [T].  ``t0`` > 0: frames < t0 are halo frames (sources only), used by the
+    timepoint sharding.  Returns an ``Association``."""
+    ctx = ops.get_context(Y.device)
+    l0 = ctx.launches
+    det = ops.decode_nms(Y, tile_yx, tilesize, conf_thr, nms_dist, cap, want_pre=want_pre)
+    T = Y.shape[0]
+    cap = det['conf'].shape[1]
+    if mask_bits is None:
+        mask_bits = ops.pack_mask(mask)
+    W = mask.shape[-1]
+    n_out = det['n_out'].cpu().numpy()          # the one host sync of the path: T int32
+    ops.raise_status(device=Y.device)
+    keys = frame_pair_keys(T, max_num_misses, t0)
+    pairs, total, _ = build_pairs(n_out, cap, keys, mask_of_frame)
+    pl, un, wc, _ = ops.cost_matrix_batch(mask_bits, W, det['yx'].view(-1, 2), pairs, max_px, want_cost)
+    return Association(det, n_out, keys, pairs, pl, un, wc, ctx.launches - l0)

@@ -1,0 +1,417 @@
+#!/usr/bin/env python
+"""Benchmark of the AxTrack association hot path (BASELINE.json metric: frame-pairs/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c2|c3|c1]
+
+One STEP = one pass of the hot path over one timelapse block: fused decode+threshold+NMS of all
+frames of the block (K1) and the A* path-length cost matrices of all its (t, t_bef) frame pairs
+(K2).  `value` = frame pairs per second with inputs resident in HBM; `e2e` = the same through the
+host-buffer C-ABI calls (numpy in / numpy out, H2D + D2H inside the timed region).
+
+N > 1 (torchrun): the timelapse is partitioned by timepoint, T frames per rank (weak scaling)
+plus a 2-frame halo that each rank decodes itself; the only collective is the gather of the
+per-pair matrices to rank 0 (NCCL send/recv), inside the timed step.
+
+--impl reference: the reference's own CPU implementation (its compiled pyastar2d fork from
+oracle/_ref driven by the reference's pair loop + ThreadPoolExecutor, and the numpy decode/NMS
+port) on the host cores, each step a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # BASELINE.json configs[1]: synthetic 2048x2048 timelapse, 100 frames, ~200 detections/frame
+    'c2': dict(H=2048, W=2048, T=100, n_dets=250, desc='configs[1]: synthetic 2048x2048 timelapse, 100 frames, ~200 dets/frame, deployed params.pkl tiling (512 px tiles, 12x12 cells)'),
+    # configs[2]: dense 4096x4096, 200 frames, ~800 dets/frame
+    'c3': dict(H=4096, W=4096, T=200, n_dets=1000, desc='configs[2]: dense synthetic 4096x4096 timelapse, 200 frames, ~800 dets/frame'),
+    # configs[0] shape (examples/test.py), 2 frames
+    'c1': dict(H=1969, W=3868, T=2, n_dets=250, desc='configs[0]: example timelapse shape 1969x3868, 2 frames'),
+}
+MAX_PX = 500          # AxonDetections.py:77
+MAX_MISSES = 1        # deployed MCF_MAX_NUM_MISSES
+
+
+# --------------------------------------------------------------------------------------------
+# synthetic workload
+# --------------------------------------------------------------------------------------------
+def make_block(wl, rank, seed=0):
+    """(mask bool[H,W], Y f32 [Tb,ntiles,12,12,3], tile_yx, t0): rank's block of the timelapse;
+    ranks > 0 carry a 2-frame halo in front (t0 = 2)."""
+    from axtrack_b200 import synth
+    H, W, T = wl['H'], wl['W'], wl['T']
+    mask = synth.make_mask(H, W, seed)
+    t0 = 0 if rank == 0 else MAX_MISSES + 1
+    tracks = synth.make_tracks(mask, wl['n_dets'], T + t0, seed + 17 * rank)
+    Y = np.stack([synth.make_head_tensor(tracks[t], H, W, seed + 1000 * rank + t)[0] for t in range(T + t0)])
+    return mask, Y, synth.tile_table(H, W), t0
+
+
+def ball_cells(dets_yx, H, W, r):
+    """|L1 ball of radius r around each detection, clipped to the image| (cells)."""
+    out = np.zeros(len(dets_yx), np.int64)
+    dy = np.arange(-r, r + 1)
+    for i, (y, x) in enumerate(np.asarray(dets_yx, np.int64)):
+        rows = y + dy
+        ok = (rows >= 0) & (rows < H)
+        hw = r - np.abs(dy)
+        lo = np.maximum(0, x - hw)
+        hi = np.minimum(W - 1, x + hw)
+        out[i] = np.maximum(0, hi - lo + 1)[ok].sum()
+    return out
+
+
+def algorithmic_bytes(frame_dets, keys, H, W, max_px):
+    """SURVEY.md 8(d) B_pair summed over the pairs: the L1 ball of radius max_px-1 of every
+    source at 1 B/cell (the uint8 mask the reference starts from) + 5 B per matrix entry
+    (int32 length + flag) + 8 B per detection."""
+    balls = [ball_cells(d, H, W, max_px - 1) for d in frame_dets]
+    tot = 0
+    for t, tb in keys:
+        tot += int(balls[tb].sum()) + len(frame_dets[tb]) * len(frame_dets[t]) * 5 + (len(frame_dets[tb]) + len(frame_dets[t])) * 8
+    return tot
+
+
+# --------------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=['nvidia-smi unavailable'])
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(',')]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), f[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+# --------------------------------------------------------------------------------------------
+# CPU reference arm
+# --------------------------------------------------------------------------------------------
+def cpu_sample(mask, frame_dets, Y, tile_yx, target_calls):
+    """One bounded sample of the reference CPU path: decode+NMS of one frame (numpy port of the
+    pandas code) + the reference pair loop over the first sources of frame pair (1, 0) until
+    ~target_calls in-range A* calls.  -> (seconds, in-range calls, kind)."""
+    import oracle
+    a, b = frame_dets[0], frame_dets[1]
+    d2 = ((a[:, None, :].astype(np.int64) - b[None, :, :]) ** 2).sum(-1)
+    inr = (d2 < MAX_PX * MAX_PX).sum(1)
+    ns = int(np.searchsorted(np.cumsum(inr), target_calls) + 1)
+    ns = max(1, min(ns, len(a)))
+    use_ref = oracle.ref_available()
+    t0 = time.perf_counter()
+    oracle.decode_stitch_nms(Y[0], tile_yx)
+    t_dec = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    if use_ref:
+        oracle.ref_cost_matrix(mask, a[:ns], b, MAX_PX, threads=True)
+    else:
+        oracle.cost_matrix_astar(mask, a[:ns], b, MAX_PX)
+    t_astar = time.perf_counter() - t0
+    return t_astar, int(inr[:ns].sum()), t_dec, ('reference' if use_ref else 'port'), ns
+
+
+def cpu_pairs_per_s(t_astar, calls, t_dec, calls_per_pair, frames_per_pair):
+    per_pair = t_astar / max(calls, 1) * calls_per_pair + t_dec * frames_per_pair
+    return 1.0 / per_pair
+
+
+def inrange_calls_per_pair(frame_dets, keys):
+    tot = 0
+    for t, tb in keys:
+        a, b = frame_dets[tb].astype(np.int64), frame_dets[t].astype(np.int64)
+        tot += int((((a[:, None, :] - b[None, :, :]) ** 2).sum(-1) < MAX_PX * MAX_PX).sum())
+    return tot / max(len(keys), 1)
+
+
+def oracle_frame_dets(Y, tile_yx):
+    import oracle
+    out = []
+    for t in range(len(Y)):
+        o = oracle.decode_stitch_nms(Y[t], tile_yx)
+        out.append(np.stack([o['y'], o['x']], 1).astype(np.int32))
+    return out
+
+
+def run_reference(args, wl):
+    from axtrack_b200.host import frame_pair_keys
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    sub = dict(wl, T=3)
+    mask, Y, tile_yx, _ = make_block(sub, 0)
+    frame_dets = oracle_frame_dets(Y, tile_yx)
+    keys = frame_pair_keys(3, MAX_MISSES)
+    cpp = inrange_calls_per_pair(frame_dets, keys)
+    T = wl['T'] * args.gpus
+    frames_per_pair = T / max(2 * T - 3, 1)
+    target = args.ref_calls
+    times = []
+    for i in range(args.warmup + args.steps):
+        t_astar, calls, t_dec, kind, ns = cpu_sample(mask, frame_dets, Y, tile_yx, target)
+        if i >= args.warmup:
+            times.append((t_astar, calls, t_dec))
+    ta = sum(x[0] for x in times); ca = sum(x[1] for x in times); td = sum(x[2] for x in times) / len(times)
+    v = cpu_pairs_per_s(ta, ca, td, cpp, frames_per_pair)
+    cores = len(os.sched_getaffinity(0))
+    sample = (f'per step: decode+NMS of 1 frame + the reference pair loop (ThreadPoolExecutor over targets, GIL-bound) '
+              f'for the first {ns} sources x {len(frame_dets[1])} targets of frame pair (1,0) = {calls} in-range A* calls; '
+              f'extrapolated linearly to {cpp:.0f} in-range calls per frame pair')
+    line = dict(metric='frame-pairs/sec (A* cost matrix + decode/NMS)', value=v, unit='frame-pairs/s', impl='reference',
+                n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * (ta + td * len(times)) / len(times), higher_is_better=True, scaling='weak',
+                vs_baseline=None, dtype='f32', data='synthetic',
+                config=dict(workload=wl['desc'], max_px=MAX_PX, max_num_misses=MAX_MISSES),
+                cpu_baseline=dict(value=v, unit='frame-pairs/s', cores=cores, kind=kind, sample=sample),
+                e2e=dict(value=v, unit='frame-pairs/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------------
+def run_b200(args, wl):
+    import torch
+    import torch.distributed as dist
+    from axtrack_b200 import ops, pipeline, host
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: axtrack_b200 has no CPU fallback')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    mask, Y, tile_yx, t0 = make_block(wl, rank)
+    H, W = mask.shape
+    Yd = torch.from_numpy(Y).to(dev)
+    td = torch.from_numpy(tile_yx).to(dev)
+    md = torch.from_numpy(mask.astype(np.uint8)).to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+    ctx = ops.get_context(dev)
+
+    recv = {}
+
+    def gather_to_rank0(res):
+        if world == 1:
+            return
+        sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(sizes, torch.tensor([res.path_len.numel()], dtype=torch.int64, device=dev))
+        opsl = []
+        if rank == 0:
+            for r in range(1, world):
+                n = int(sizes[r].item())
+                if r not in recv or recv[r][0].numel() < n:
+                    recv[r] = (torch.empty(n, dtype=torch.int32, device=dev), torch.empty(n, dtype=torch.uint8, device=dev))
+                opsl += [dist.P2POp(dist.irecv, recv[r][0][:n], r), dist.P2POp(dist.irecv, recv[r][1][:n], r)]
+        else:
+            opsl += [dist.P2POp(dist.isend, res.path_len, 0), dist.P2POp(dist.isend, res.unreachable, 0)]
+        for w in dist.batch_isend_irecv(opsl):
+            w.wait()
+
+    def step():
+        res = pipeline.associate_frames(Yd, td, md, max_px=MAX_PX, max_num_misses=MAX_MISSES, want_cost=False, t0=t0)
+        gather_to_rank0(res)
+        return res
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        res = step()
+    n_pairs = len(res.keys)
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx.launches
+    evs = []
+    sync_all()
+    for _ in range(args.steps):
+        flush.fill_(1)                                   # L2 flush between timed iterations (untimed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = step()
+        e1.record()
+        evs.append((e0, e1))
+    sync_all()
+    launches = ctx.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([ms, float(n_pairs)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+        ms, total_pairs = float(tm[0]), float(ts[1])
+    else:
+        total_pairs = float(n_pairs)
+    value = total_pairs * args.steps / (ms * 1e-3)
+
+    # ---- dominant kernel alone (K2) for the roofline: CUDA events around the launch ------------
+    bits = ops.pack_mask(md)
+    det = ops.decode_nms(Yd, td)
+    n_out = det['n_out'].cpu().numpy()
+    cap = det['conf'].shape[1]
+    pairs, total, _ = pipeline.build_pairs(n_out, cap, res.keys)
+    pairs_dev = torch.from_numpy(pairs.view(np.uint8).reshape(-1).copy()).to(dev)
+    outb = (torch.empty(max(total, 1), dtype=torch.int32, device=dev), torch.empty(max(total, 1), dtype=torch.uint8, device=dev), None)
+    yx = det['yx'].view(-1, 2)
+    k2ms = []
+    for i in range(3 + args.steps):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.cost_matrix_batch(bits, W, yx, pairs, MAX_PX, want_cost=False, out=outb, pairs_dev=pairs_dev)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            k2ms.append(e0.elapsed_time(e1))
+    k1ms = []
+    for i in range(3 + args.steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.decode_nms(Yd, td, want_pre=False)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            k1ms.append(e0.elapsed_time(e1))
+    yx_h = det['yx'].cpu().numpy()
+    frame_dets = [yx_h[t, :int(n_out[t])] for t in range(len(n_out))]
+    alg = algorithmic_bytes(frame_dets, res.keys, H, W, MAX_PX)
+    k2 = float(np.mean(k2ms)) * 1e-3
+    peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    traffic = None
+    tf = os.path.join(ROOT, 'profiles', 'k2_dram_traffic.json')
+    if os.path.exists(tf):
+        try:
+            traffic = json.load(open(tf)).get(args.workload)
+        except Exception:
+            traffic = None
+    roofline = dict(bound='hbm', kernel='k2_search_kernel (one launch = all frame pairs of the block)',
+                    achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
+                    peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
+                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)),
+                    traffic=traffic)
+
+    # ---- e2e: host buffers through the C ABI ------------------------------------------------------
+    e2e = None
+    cpu = None
+    if True:
+        ha = host.HostAssociator(local)
+        pin = lambda a: torch.from_numpy(a).pin_memory().numpy()
+        Yh, th, mh = pin(Y), pin(tile_yx), pin(mask.astype(np.uint8))
+        F = Y.shape[0]
+        dout = dict(n_pre=pin(np.zeros(F, np.int32)), n_out=pin(np.zeros(F, np.int32)), conf=pin(np.empty((F, cap), np.float32)),
+                    yx=pin(np.empty((F, cap, 2), np.int32)), keep_idx=pin(np.empty((F, cap), np.int32)))
+        mout = (pin(np.empty(max(total, 1), np.int32)), pin(np.empty(max(total, 1), np.uint8)), None)
+
+        def e2e_step():
+            d = ha.decode_nms(Yh, th, out=dout)
+            prs, tot, _ = pipeline.build_pairs(d['n_out'], cap, res.keys)
+            ha.cost_matrices_flat(mh, d['yx'].reshape(-1, 2), prs, tot, MAX_PX, want_cost=False, out=mout)
+            return tot
+        for _ in range(3):
+            tot = e2e_step()
+        sync_all()
+        t_0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t_0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        h2d = Yh.nbytes + th.nbytes + mh.nbytes + F * cap * 8 + len(res.keys) * 32
+        d2h = sum(v.nbytes for v in dout.values()) + tot * 5
+        e2e = dict(value=total_pairs * args.steps / float(tt[0]), unit='frame-pairs/s', h2d_bytes_per_step=int(h2d),
+                   d2h_bytes_per_step=int(d2h), ms_per_step=1e3 * float(tt[0]) / args.steps,
+                   api='axb_decode_nms_host + axb_cost_matrix_batch_host (numpy in/out, pinned)')
+        # parity spot check of what was timed (oracle as checker only)
+        assert np.array_equal(mout[0][:tot], res.path_len.cpu().numpy()) and np.array_equal(mout[1][:tot], res.unreachable.cpu().numpy())
+
+    if rank == 0 and world == 1:
+        t_astar, calls, t_dec, kind, ns = cpu_sample(mask, frame_dets, Y, tile_yx, args.cpu_calls)
+        cpp = inrange_calls_per_pair(frame_dets, res.keys)
+        v = cpu_pairs_per_s(t_astar, calls, t_dec, cpp, len(frame_dets) / max(len(res.keys), 1))
+        cpu = dict(value=v, unit='frame-pairs/s', cores=len(os.sched_getaffinity(0)), kind=kind,
+                   sample=(f'{t_astar:.1f} s: reference pair loop (compiled pyastar2d fork + ThreadPoolExecutor over targets, GIL-bound) '
+                           f'for the first {ns} sources of frame pair (1,0) = {calls} in-range A* calls, + numpy decode/NMS of 1 frame '
+                           f'({t_dec * 1e3:.1f} ms); extrapolated to {cpp:.0f} in-range calls per frame pair'))
+
+    if rank == 0:
+        line = dict(metric='frame-pairs/sec (A* cost matrix + decode/NMS)', value=value, unit='frame-pairs/s', n_gpus=world,
+                    steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms / args.steps, higher_is_better=True,
+                    scaling='weak', vs_baseline=None, dtype='int32', data='synthetic',
+                    config=dict(workload=wl['desc'], frames_per_gpu=wl['T'], frame_pairs_total=int(total_pairs),
+                                dets_per_frame=float(np.mean(n_out)), max_px=MAX_PX, max_num_misses=MAX_MISSES,
+                                parallelism=f'timepoint shards x{world}, gather to rank 0', l2='flushed between timed steps (256 MiB write)'),
+                    e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
+    ap.add_argument('--cpu-calls', type=int, default=1200, help='in-range A* calls of the cpu_baseline sample (~15 ms each at 2048^2)')
+    ap.add_argument('--ref-calls', type=int, default=250, help='in-range A* calls per --impl reference step')
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == 'reference':
+        run_reference(args, wl)
+    else:
+        run_b200(args, wl)
+
+
+if __name__ == '__main__':
+    main()

@@ -134,17 +134,31 @@ int axb_cost_matrix_host(axb_ctx* ctx, const uint8_t* mask_host, int H, int W,
  * tile_yx_dev int32 [ntiles, 2] (tile_y, tile_x) of each compact tile (Timelapse.py:141-148)
  * Outputs (cap = row pitch; AXB_ERR_CAPACITY is set if a frame has more candidates):
  *   pre_*     the stitched pre-NMS frame detections in the reference's concat order
- *             (tile-major; inside a tile conf ascending): conf, (x, y) frame coords, tile index
+ *             (tile-major; inside a tile conf ascending): conf [F,cap], frame coords
+ *             [F,cap,2] as (y, x) -- the row layout axb_cost_matrix_batch reads --, tile [F,cap]
  *   n_pre     int32 [F]
- *   conf/xy   NMS survivors in conf-descending order; keep_idx = their pre-NMS indices
+ *   conf/yx   NMS survivors in conf-descending order ([F,cap], [F,cap,2] rows (y, x));
+ *             keep_idx = their pre-NMS indices ("survivor indices")
  *   n_out     int32 [F]
- * Any of the pre_* pointers may be NULL. */
+ * Any of the pre_* pointers may be NULL.  The yx output can be passed as dets_yx_dev to
+ * axb_cost_matrix_batch unchanged (frame f's detections start at row f*cap). */
 int axb_decode_nms(axb_ctx* ctx, const float* Y_dev, const int32_t* tile_yx_dev,
                    int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist,
                    int cap,
-                   float* pre_conf_dev, int32_t* pre_xy_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
-                   float* conf_dev, int32_t* xy_dev, int32_t* keep_idx_dev, int32_t* n_out_dev,
+                   float* pre_conf_dev, int32_t* pre_yx_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
+                   float* conf_dev, int32_t* yx_dev, int32_t* keep_idx_dev, int32_t* n_out_dev,
                    void* stream);
+
+/* Same with HOST buffers (Y, tile table and every output in host memory; pre_* may be NULL):
+ * host->device copy of the head tensor, the fused kernel, device->host copies of the results on
+ * the ctx's own stream, then synchronises and returns the sticky status (AXB_ERR_CAPACITY).
+ * This is the call a non-torch binding of the per-frame loop body AxonDetections.py:122-128
+ * makes for all frames at once. */
+int axb_decode_nms_host(axb_ctx* ctx, const float* Y_host, const int32_t* tile_yx_host,
+                        int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist,
+                        int cap,
+                        float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_tile_host, int32_t* n_pre_host,
+                        float* conf_host, int32_t* yx_host, int32_t* keep_idx_host, int32_t* n_out_host);
 
 /* ---- status ----------------------------------------------------------------------------
  * Synchronises `stream` and returns the sticky device-side status of the calls issued on this

@@ -1,0 +1,245 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the committed golden
+fixtures produced by the unmodified reference.  Bit-exact: path lengths, unreachable flags,
+NMS survivor indices, decoded coordinates; weighted path cost within 1e-5 relative."""
+import ctypes
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from axtrack_b200 import synth
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5      # north_star: float-weighted path costs agree within 1e-5 relative
+
+
+@pytest.fixture(scope='module')
+def cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail('-m gpu tests need a CUDA device (no CPU fallback exists)')
+    torch.cuda.set_device(0)
+    return torch
+
+
+def _gpu_cost(torch, mask, src, dst, max_px):
+    from axtrack_b200 import ops
+    bits = ops.pack_mask(torch.from_numpy(np.ascontiguousarray(mask, dtype=np.uint8)).cuda())
+    pl, un, wc = ops.cost_matrix(bits, mask.shape[1], torch.from_numpy(np.ascontiguousarray(src, dtype=np.int32)).cuda(),
+                                 torch.from_numpy(np.ascontiguousarray(dst, dtype=np.int32)).cuda(), max_px)
+    ops.raise_status()
+    return pl.cpu().numpy(), un.cpu().numpy(), wc.cpu().numpy()
+
+
+def _check(got, ref, tag=''):
+    pl, un, wc = got
+    assert np.array_equal(pl, ref[0]), tag
+    assert np.array_equal(un, ref[1]), tag
+    ok = ref[1] == 0
+    assert np.all(np.isinf(wc[~ok])), tag
+    assert np.allclose(wc[ok], np.asarray(ref[2])[ok], rtol=RTOL, atol=0), tag
+
+
+def test_pack_mask(cuda):
+    from axtrack_b200 import ops
+    rng = np.random.default_rng(0)
+    for H, W in [(5, 7), (33, 64), (40, 100), (64, 2048), (3, 16), (17, 48)]:
+        m = (rng.random((2, H, W)) < 0.4).astype(np.uint8)
+        m[0, 0, 0] = 2          # only == 1 is on the mask (AxonDetections.py:598)
+        bits = ops.pack_mask(cuda.from_numpy(m).cuda()).cpu().numpy().view(np.uint32)
+        exp = np.zeros((2, H, (W + 31) // 32), np.uint32)
+        for x in range(W):
+            exp[:, :, x >> 5] |= (m[:, :, x] == 1).astype(np.uint32) << np.uint32(x & 31)
+        assert np.array_equal(bits, exp), (H, W)
+        w = np.where(m == 1, 1, 2 ** 16).astype(np.float32)
+        bits2 = ops.pack_weights(cuda.from_numpy(w).cuda()).cpu().numpy().view(np.uint32)
+        assert np.array_equal(bits2, exp), (H, W)
+        ops.raise_status()
+
+
+def test_golden_astar(cuda, golden_dir):
+    files = sorted(glob.glob(os.path.join(golden_dir, 'astar_s*.npz')))
+    assert len(files) >= 4
+    for f in files:
+        g = np.load(f)
+        H, W, max_px = int(g['H']), int(g['W']), int(g['max_px'])
+        mask = np.unpackbits(g['mask_bits'])[:H * W].reshape(H, W)
+        for t, tb in g['keys']:
+            got = _gpu_cost(cuda, mask, g[f'dets_yx_{tb}'], g[f'dets_yx_{t}'], max_px)
+            _check(got, (g[f'dist_{t}_{tb}'], g[f'none_{t}_{tb}'], g[f'wcost_{t}_{tb}']), (f, t, tb))
+            # downstream "final cost matrix" (transition_model, mincostflow_models.py:100-119)
+            tc = oracle.transition_cost(got[0], max_px, 0.6, int(t - tb))
+            ref_t = g[f'tcost_{t}_{tb}']
+            assert np.array_equal(np.isinf(tc), np.isinf(ref_t))
+            fin = ~np.isinf(tc)
+            assert np.allclose(tc[fin], ref_t[fin], rtol=RTOL, atol=0)
+
+
+def test_golden_decode_nms(cuda, golden_dir):
+    from axtrack_b200 import ops
+    for f in sorted(glob.glob(os.path.join(golden_dir, 'decode_nms_s*.npz'))):
+        g = np.load(f)
+        o = ops.decode_nms(cuda.from_numpy(g['Y']).cuda(), cuda.from_numpy(g['tile_yx'].astype(np.int32)).cuda(),
+                           int(g['tilesize']), float(g['conf_thr']), int(g['nms_dist']))
+        ops.raise_status()
+        npre, nout = int(o['n_pre'][0]), int(o['n_out'][0])
+        assert npre == len(g['pre_conf']) and nout == len(g['conf']), f
+        assert np.array_equal(o['pre_conf'][0, :npre].cpu().numpy(), g['pre_conf'])
+        pyx = o['pre_yx'][0, :npre].cpu().numpy()
+        assert np.array_equal(pyx[:, 1], g['pre_x']) and np.array_equal(pyx[:, 0], g['pre_y'])
+        assert np.array_equal(o['keep_idx'][0, :nout].cpu().numpy(), g['keep_idx'])
+        assert np.array_equal(o['conf'][0, :nout].cpu().numpy(), g['conf'])
+        yx = o['yx'][0, :nout].cpu().numpy()
+        assert np.array_equal(yx[:, 1], g['x']) and np.array_equal(yx[:, 0], g['y'])
+
+
+@pytest.mark.parametrize('seed', [0, 1, 2, 3])
+def test_cost_matrix_vs_oracle_random(cuda, seed):
+    """Small adversarial grids: gaps, off-mask detections, short cut-offs; vs the closed form AND
+    the per-pair restated A*."""
+    rng = np.random.default_rng(100 + seed)
+    for it in range(25):
+        H, W = int(rng.integers(20, 160)), int(rng.integers(20, 160))
+        m = np.zeros((H, W), bool)
+        for _ in range(int(rng.integers(2, 7))):
+            y = int(rng.integers(0, H)); w_ = int(rng.integers(1, 6)); m[y:y + w_, :] = True
+            x = int(rng.integers(0, W)); w_ = int(rng.integers(1, 6)); m[:, x:x + w_] = True
+        for _ in range(int(rng.integers(0, 8))):
+            y, x, g = int(rng.integers(0, H)), int(rng.integers(0, W)), int(rng.integers(1, 5))
+            m[y:y + g, x:x + g] = False
+        max_px = int(rng.choice([1, 2, 12, 25, 40, 80, 150, 500, 511]))
+        fg = np.argwhere(m)
+
+        def pick(n):
+            p = fg[rng.integers(0, len(fg), n)] + rng.integers(-2, 3, (n, 2)) * (rng.random((n, 1)) < 0.3)
+            p[:, 0] = np.clip(p[:, 0], 0, H - 1)
+            p[:, 1] = np.clip(p[:, 1], 0, W - 1)
+            return p.astype(np.int32)
+        src, dst = pick(int(rng.integers(1, 9))), pick(int(rng.integers(1, 14)))
+        got = _gpu_cost(cuda, m, src, dst, max_px)
+        _check(got, oracle.cost_matrix_rule(m, src, dst, max_px), (seed, it, 'rule'))
+
+
+def test_cost_matrix_edge_cases(cuda):
+    from axtrack_b200 import ops
+    m = np.ones((1, 20), np.uint8)
+    # SURVEY Appendix A known answer: 1x20 row, max=19 -> None, max=20 -> 20
+    pl, un, _ = _gpu_cost(cuda, m, [[0, 0]], [[0, 19]], 19)
+    assert pl[0, 0] == 19 and un[0, 0] == 1
+    pl, un, wc = _gpu_cost(cuda, m, [[0, 0]], [[0, 19]], 20)
+    assert pl[0, 0] == 20 and un[0, 0] == 0 and wc[0, 0] == 19.0
+    # source == target -> path of one pixel (astar.cpp:67,99-102)
+    pl, un, wc = _gpu_cost(cuda, m, [[0, 5]], [[0, 5]], 500)
+    assert pl[0, 0] == 1 and un[0, 0] == 0 and wc[0, 0] == 0.0
+    # pyastar2d/tests/test_astar.py:63-78 narrow grids
+    for shp, a, b in [((5, 1), (0, 0), (4, 0)), ((1, 5), (0, 0), (0, 4))]:
+        pl, un, _ = _gpu_cost(cuda, np.ones(shp, np.uint8), [a], [b], 500)
+        assert pl[0, 0] == 5 and un[0, 0] == 0
+    # empty inputs
+    bits = ops.pack_mask(cuda.from_numpy(m).cuda())
+    e = cuda.zeros((0, 2), dtype=cuda.int32, device='cuda')
+    one = cuda.zeros((1, 2), dtype=cuda.int32, device='cuda')
+    assert ops.cost_matrix(bits, 20, e, one)[0].shape == (0, 1)
+    assert ops.cost_matrix(bits, 20, one, e)[0].shape == (1, 0)
+    # all-background mask: every step costs 65536 (levels only)
+    z = np.zeros((30, 30), np.uint8)
+    src, dst = np.array([[3, 3], [15, 15]], np.int32), np.array([[3, 9], [20, 11], [29, 29]], np.int32)
+    _check(_gpu_cost(cuda, z, src, dst, 40), oracle.cost_matrix_rule(z, src, dst, 40))
+    _check(_gpu_cost(cuda, z, src, dst, 40), oracle.cost_matrix_astar(z, src, dst, 40))
+
+
+def test_out_of_grid_errors(cuda):
+    """astar_wrapper.py:39-45 -> the same ValueError text, first offender in reference order."""
+    from axtrack_b200 import ops
+    m = np.ones((50, 60), np.uint8)
+    bits = ops.pack_mask(cuda.from_numpy(m).cuda())
+    pairs, total, nsrc = ops.make_pairs([(0, 0, 2, 2, 2)])
+    for dets, msg in [(np.array([[5, 5], [50, 3], [6, 6], [7, 7]], np.int32), r'Start of \(50, 3\) lies outside grid'),
+                      (np.array([[5, 5], [8, 3], [6, 6], [7, -1]], np.int32), r'Goal of \(7, -1\) lies outside grid')]:
+        ops.cost_matrix_batch(bits, 60, cuda.from_numpy(dets).cuda(), pairs, 500)
+        with pytest.raises(ValueError, match=msg):
+            ops.raise_status(pairs, dets)
+        ops.raise_status()      # cleared
+    # out-of-grid but out of Euclid range: the reference never calls pyastar2d -> no error
+    dets = np.array([[5, 5], [6, 6], [7, 7], [900, 900]], np.int32)
+    pl, un, _, _ = ops.cost_matrix_batch(bits, 60, cuda.from_numpy(dets).cuda(), pairs, 500)
+    ops.raise_status(pairs, dets)
+    assert un.cpu().numpy().reshape(2, 2)[:, 1].all()
+    # weights < 1 (astar_wrapper.py:35-37)
+    w = np.ones((8, 8), np.float32); w[2, 2] = 0.25
+    ops.pack_weights(cuda.from_numpy(w).cuda())
+    with pytest.raises(ValueError, match='Minimum cost to move must be 1'):
+        ops.raise_status()
+
+
+@pytest.mark.parametrize('seed', [0, 1])
+def test_timelapse_pipeline_vs_oracle(cuda, seed):
+    """decode+NMS of all frames then all (t, t_bef) cost matrices, vs the oracle; corridor mask."""
+    from axtrack_b200.pipeline import associate_frames
+    H, W, T = 1024, 1536, 4
+    mask = synth.make_mask(H, W, seed, pitch=(90, 200), width=(6, 16))
+    tracks = synth.make_tracks(mask, 70, T, seed, off_mask_frac=0.08)
+    Y = np.stack([synth.make_head_tensor(tracks[t], H, W, seed * 10 + t)[0] for t in range(T)])
+    tt = synth.tile_table(H, W)
+    res = associate_frames(cuda.from_numpy(Y).cuda(), cuda.from_numpy(tt).cuda(),
+                           cuda.from_numpy(mask.astype(np.uint8)).cuda())
+    dets = []
+    for t in range(T):
+        o = oracle.decode_stitch_nms(Y[t], tt)
+        d = res.frame_dets(t)
+        for k in ('conf', 'x', 'y', 'keep_idx'):
+            assert np.array_equal(d[k], o[k]), (t, k)
+        dets.append(np.stack([o['y'], o['x']], 1).astype(np.int32))
+    mats = res.pair_matrices()
+    assert list(mats) == [(1, 0), (2, 1), (2, 0), (3, 2), (3, 1)]
+    for (t, tb), got in mats.items():
+        _check(got, oracle.cost_matrix_rule(mask, dets[tb], dets[t], 500), (t, tb))
+
+
+def test_host_entry_points(cuda):
+    """axb_decode_nms_host / axb_cost_matrix_batch_host: numpy in, numpy out (what e2e times)."""
+    from axtrack_b200 import host
+    H, W, T = 640, 900, 3
+    mask = synth.make_mask(H, W, 5, pitch=(70, 160), width=(6, 14))
+    tracks = synth.make_tracks(mask, 40, T, 5, off_mask_frac=0.1)
+    Y = np.stack([synth.make_head_tensor(tracks[t], H, W, 50 + t)[0] for t in range(T)])
+    tt = synth.tile_table(H, W)
+    ha = host.HostAssociator(0)
+    det = ha.decode_nms(Y, tt)
+    dets = []
+    for t in range(T):
+        o = oracle.decode_stitch_nms(Y[t], tt)
+        n = int(det['n_out'][t])
+        assert np.array_equal(det['keep_idx'][t, :n], o['keep_idx'])
+        assert np.array_equal(det['yx'][t, :n, 0], o['y']) and np.array_equal(det['yx'][t, :n, 1], o['x'])
+        dets.append(det['yx'][t, :n])
+    mats = ha.cost_matrices(mask.astype(np.uint8), dets, max_px=500, max_num_misses=1)
+    for (t, tb), got in mats.items():
+        _check(got, oracle.cost_matrix_rule(mask, dets[tb], dets[t], 500), (t, tb))
+
+
+def test_full_size_properties(cuda):
+    """BASELINE config-2 sizes (2048^2, ~200 dets): size-independent properties -- symmetry of
+    on-mask/on-mask path lengths where both directions are reachable, self distance 1, the
+    Euclid pre-filter, L >= L1+1, and agreement with the closed-form oracle on a row sample."""
+    H = W = 2048
+    mask = synth.make_mask(H, W, 0)
+    a, b = synth.make_tracks(mask, 200, 2, 0, off_mask_frac=0.0)
+    pl, un, wc = _gpu_cost(cuda, mask, a, b, 500)
+    pl2, un2, _ = _gpu_cost(cuda, mask, b, a, 500)
+    both = (un == 0) & (un2.T == 0)
+    assert both.sum() > 500
+    assert np.array_equal(pl[both], pl2.T[both])
+    d2 = ((a[:, None, :].astype(np.int64) - b[None, :, :]) ** 2).sum(-1)
+    assert un[d2 >= 500 * 500].all() and (pl[un == 1] == 500).all()
+    l1 = np.abs(a[:, None, :].astype(np.int64) - b[None, :, :]).sum(-1)
+    assert (pl[un == 0] >= l1[un == 0] + 1).all() and (pl[un == 0] <= 500).all()
+    # level-0 paths cost exactly L-1
+    lvl0 = (un == 0) & (wc < 65536)
+    assert np.array_equal(wc[lvl0], (pl[lvl0] - 1).astype(np.float32))
+    pls, uns, _ = _gpu_cost(cuda, mask, a, a, 500)
+    assert (np.diag(pls) == 1).all() and (np.diag(uns) == 0).all()
+    rows = np.arange(0, len(a), 9)
+    _check((pl[rows], un[rows], wc[rows]), oracle.cost_matrix_rule(mask, a[rows], b, 500))
