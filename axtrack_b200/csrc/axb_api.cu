@@ -19,9 +19,11 @@ struct axb_ctx {
     unsigned long long* status_host = nullptr;   // pinned
 
     // K2
-    uint32_t* k2_scratch = nullptr;   int k2_scratch_ctas = 0;
-    int* work_counter = nullptr;
-    int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;
+    uint32_t* k2_fast_scratch = nullptr;   int k2_fast_ctas = 0;
+    uint32_t* k2_gen_scratch = nullptr;    int k2_gen_ctas = 0;
+    int* counters = nullptr;
+    int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;   // [work | all | next] x prefix_cap
+    int* gen_list = nullptr;          size_t gen_list_bytes = 0;
     // K1
     uint8_t* k1_scratch = nullptr;    size_t k1_scratch_bytes = 0;
     // staging for the single-pair and host entry points
@@ -59,20 +61,23 @@ int grow(axb_ctx* c, T** ptr, size_t* have, size_t need) {
     return AXB_OK;
 }
 
-int ensure_k2(axb_ctx* c, int n_pairs) {
-    if (!c->k2_scratch) {
-        const size_t bytes = (size_t)c->num_sms * 4 * axb::kGCap * sizeof(uint32_t);
-        AXB_CUDA(c, cudaMalloc((void**)&c->k2_scratch, bytes));
-        c->k2_scratch_ctas = c->num_sms;
+int ensure_k2(axb_ctx* c, int n_pairs, int total_src) {
+    if (!c->k2_fast_scratch) {
+        c->k2_fast_ctas = c->num_sms * axb::kFastCtasPerSm;
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_fast_scratch, (size_t)c->k2_fast_ctas * axb::kFastScratchWords * sizeof(uint32_t)));
     }
-    if (!c->work_counter) AXB_CUDA(c, cudaMalloc((void**)&c->work_counter, 256));
+    if (!c->k2_gen_scratch) {
+        c->k2_gen_ctas = c->num_sms;
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_gen_scratch, (size_t)c->k2_gen_ctas * axb::kGenScratchWords * sizeof(uint32_t)));
+    }
+    if (!c->counters) AXB_CUDA(c, cudaMalloc((void**)&c->counters, 256));
     if (n_pairs + 1 > c->prefix_cap) {
         if (c->prefix_dev) AXB_CUDA(c, cudaFree(c->prefix_dev));
         c->prefix_dev = nullptr;
         c->prefix_cap = std::max(n_pairs + 1, 1024) * 2;
-        AXB_CUDA(c, cudaMalloc((void**)&c->prefix_dev, (size_t)c->prefix_cap * sizeof(int)));
+        AXB_CUDA(c, cudaMalloc((void**)&c->prefix_dev, 3 * (size_t)c->prefix_cap * sizeof(int)));
     }
-    return AXB_OK;
+    return grow(c, &c->gen_list, &c->gen_list_bytes, (size_t)std::max(total_src, 1) * sizeof(int));
 }
 
 }  // namespace
@@ -108,7 +113,8 @@ void axb_destroy(axb_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
-    cudaFree(c->k2_scratch); cudaFree(c->work_counter); cudaFree(c->prefix_dev); cudaFree(c->k1_scratch);
+    cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
+    cudaFree(c->gen_list); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
     cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -153,19 +159,23 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
         return bad_arg(c, "axb_cost_matrix_batch: NULL pointer");
     AXB_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t s = (cudaStream_t)stream;
-    int rc = ensure_k2(c, n_pairs);
+    int rc = ensure_k2(c, n_pairs, total_src);
     if (rc != AXB_OK) return rc;
-    AXB_CUDA(c, cudaMemsetAsync(c->work_counter, 0, sizeof(int), s));
-    axb::launch_work_prefix(pairs_dev, n_pairs, c->prefix_dev, s);
+    int* const work_prefix = c->prefix_dev;
+    int* const all_prefix = c->prefix_dev + c->prefix_cap;
+    int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
+    axb::launch_k2_prep(pairs_dev, n_pairs, work_prefix, all_prefix, next_same, c->counters, s);
     c->last_n_pairs = n_pairs;
     axb::K2Params p;
     p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = (W + 31) / 32;
-    p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs; p.work_prefix = c->prefix_dev;
+    p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs;
+    p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
     p.max_px = max_px; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
-    p.scratch = c->k2_scratch; p.work_counter = c->work_counter; p.err_key = c->status_dev;
-    const int grid = std::max(1, std::min(c->k2_scratch_ctas, total_src));
-    axb::launch_k2(p, grid, s);
-    c->launches += 2;
+    p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
+    p.counters = c->counters; p.gen_list = c->gen_list; p.err_key = c->status_dev;
+    axb::launch_k2_fast(p, std::max(1, std::min(c->k2_fast_ctas, total_src)), s);
+    axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
+    c->launches += 3;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;
 }
@@ -359,7 +369,7 @@ int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
             const int n = c->last_n_pairs;
             if (n > 0 && c->prefix_dev) {
                 std::vector<int> pre((size_t)n + 1);
-                AXB_CUDA(c, cudaMemcpy(pre.data(), c->prefix_dev, ((size_t)n + 1) * sizeof(int), cudaMemcpyDeviceToHost));
+                AXB_CUDA(c, cudaMemcpy(pre.data(), c->prefix_dev + c->prefix_cap, ((size_t)n + 1) * sizeof(int), cudaMemcpyDeviceToHost));
                 int lo = (int)(std::upper_bound(pre.begin(), pre.begin() + n, (int)item) - pre.begin()) - 1;
                 lo = std::max(lo, 0);
                 info[0] = lo; info[1] = item - pre[lo];

@@ -9,19 +9,27 @@ namespace axb {
 
 // ---- K2 geometry ---------------------------------------------------------------------------
 // Search window of one source: the L1 ball of radius RW = max_px around it (cells at hop
-// max_px are detected, cells at hop <= max_px-1 are expanded).  The diamond is stored FOLDED:
-// rows dy <= 0 live in folded row dy+RW centred at column 512, rows dy > 0 share folded row
-// dy-1 centred at column 0 (mod 1024).  Both halves of a folded row together hold 2*RW cells,
-// so the whole window is (RW+1) rows x 1024 bits: 64 KB per bitmap at max_px = 500 instead of
-// 125 KB for the bounding box.
+// max_px are detected, cells at hop <= max_px-1 are expanded).  The diamond is stored FOLDED
+// on a circle of 1024 columns: rows dy <= 0 live in folded row dy+RW with their centre at
+// column 512, rows dy > 0 share folded row dy-1 with their centre at column 0; columns are
+// measured from the 32-pixel-aligned word that holds the source (cx = x - (sx & ~31)), so one
+// shared-memory word is one aligned word of the packed mask.  Both halves of a folded row
+// together hold 2*RW <= 1022 cells, so the window is (RW+1) rows x 1024 bits: 64 KB per
+// bitmap at max_px = 500 instead of 125 KB for the bounding box.
 constexpr int kRowBits = 1024;
 constexpr int kRowWords = 32;
-constexpr int kK2Threads = 256;
-constexpr int kQCap = 4096;          // frontier entries kept in shared memory per buffer
-constexpr int kTCap = 2048;          // in-range targets per pass kept in shared memory
-constexpr int kGCap = 1 << 19;       // per-CTA global overflow entries (>= cells of the window)
-constexpr int kSeedEnd = 512;        // entries of the per-level seed calendar (j <= max_px)
-constexpr uint32_t kUnset = 0xFFFFFFFFu;
+constexpr int kMaxChain = 4;          // frame pairs that share one source search
+constexpr int kHashSize = 1024;       // target-cell hash (u32 entries) in shared memory
+constexpr int kHashMaxLoad = 640;     // candidates per search pass
+constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
+// fast kernel (level 0 only): one warp per source, 3 CTAs per SM
+constexpr int kFastQCap = 768;        // frontier entries per buffer in shared memory
+constexpr int kFastGQCap = 16384;     // per-CTA global overflow entries per buffer
+constexpr int kFastCtasPerSm = 3;
+// general kernel (all levels): one warp per source, both bitmaps, 1 CTA per SM
+constexpr int kGenQCap = 2048;
+constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
+constexpr uint32_t kEmpty = 0xFFFFFFFFu;
 
 struct K2Params {
     const uint32_t* mask_bits;   // [n_masks][H][Wp]
@@ -29,23 +37,33 @@ struct K2Params {
     const int32_t* dets_yx;      // [n][2] (y, x)
     const axb_pair_desc* pairs;  // device
     int n_pairs;
-    const int* work_prefix;      // [n_pairs+1] exclusive prefix of n_src (device)
+    const int* work_prefix;      // [n_pairs+1] exclusive prefix of n_src over chain LEADERS
+    const int* all_prefix;       // [n_pairs+1] exclusive prefix of n_src over all pairs (error order)
+    const int* next_same;        // [n_pairs] next pair with the same (mask, sources), or -1
     int max_px;
     int32_t* path_len;
     uint8_t* unreachable;
     float* wcost;
-    uint32_t* scratch;           // per CTA: 4 * kGCap words
-    int* work_counter;           // atomic ticket
-    unsigned long long* err_key; // atomicMin: (work item << 26 | target << 2 | code)
+    uint32_t* fast_scratch;      // per fast CTA: kCandCap + 2*kFastGQCap words
+    uint32_t* gen_scratch;       // per general CTA: kCandCap + 4*kGCap words
+    int* counters;               // [0] fast ticket, [1] general list length, [2] general ticket
+    int* gen_list;               // work items deferred to the general kernel
+    unsigned long long* err_key; // atomicMin: (item in reference order << 26 | target << 2 | code)
 };
 
-inline size_t k2_smem_bytes(int max_px) {
-    const size_t nrows = (size_t)max_px + 1;
-    return (2 * nrows * kRowWords + 2 * kQCap + 2 * kSeedEnd + 3 * kTCap) * sizeof(uint32_t);
+inline size_t k2_fast_smem_bytes(int max_px) {
+    return ((size_t)(max_px + 1) * kRowWords + 2 * kFastQCap + kHashSize) * sizeof(uint32_t);
 }
+inline size_t k2_gen_smem_bytes(int max_px) {
+    return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize) * sizeof(uint32_t);
+}
+constexpr size_t kFastScratchWords = (size_t)kCandCap + 2 * (size_t)kFastGQCap;
+constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
 
-void launch_k2(const K2Params& p, int grid, cudaStream_t stream);
-void launch_work_prefix(const axb_pair_desc* pairs, int n_pairs, int* prefix, cudaStream_t stream);
+void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
+                    int* next_same, int* counters, cudaStream_t stream);
+void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
+void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);
 void launch_pack_mask_f32(const float* w, int n_masks, int H, int W, uint32_t* bits,
                           unsigned long long* err_flags, cudaStream_t s);

@@ -2,32 +2,47 @@
 //
 // Replaces the per-pair A* of the reference (pyastar2d/src/cpp/astar.cpp:46-172 driven by
 // axtrack/AxonDetections.py:553-579,600-629): ONE bounded search per SOURCE detection answers
-// every target of that source.
+// every target of that source -- and, when several frame pairs share the same source frame and
+// mask (t_bef is the predecessor of both t_bef+1 and t_bef+2, AxonDetections.py:560), every
+// target of all of them ("chain", up to kMaxChain pairs).
 //
-// Semantics (DESIGN.md "K2 semantics"; validated against the compiled reference in
-// tests/test_oracle_golden.py).  Weights are 1 on the mask and 65536 off it
-// (AxonDetections.py:598), so the exact cost of a path is n_fg + 65536*n_bg over the pixels it
-// enters and its hop count is n_fg + n_bg.  Cells are settled in lexicographic (n_bg, n_fg)
-// order: "level" k = n_bg, and inside a level a breadth-first wave over mask pixels indexed by
-// j = n_fg.  Off-mask neighbours of level-k cells seed level k+1 with the j of the cell that
-// touched them first.  A cell at hop == max_px is never expanded (the reference pushes it with
-// path_length max_px+1, astar.cpp:136, and aborts when it reaches the top of the heap,
-// astar.cpp:88-92).  The search stops after the first level k* that contains such a cell:
-// every target of a higher level is "None" because that heap entry has a smaller priority than
-// any goal of a higher level (65536 >> 2*max_px).  Targets settled at (k, j), k <= k*, get
+// Semantics (DESIGN.md "K2 semantics"; the closed form oracle/astar_oracle.cpp implements and
+// tests/test_oracle_golden.py pins to the compiled reference).  Weights are 1 on the mask and
+// 65536 off it (AxonDetections.py:598), so the exact cost of a path is n_fg + 65536*n_bg over the
+// pixels it enters and its hop count is n_fg + n_bg.  Cells are settled in lexicographic
+// (n_bg, n_fg) order: "level" k = n_bg, and inside a level a breadth-first wave over mask pixels
+// indexed by j = n_fg.  Off-mask neighbours of level-k cells seed level k+1 with the j of the
+// cell that touched them first.  A cell at hop == max_px is never expanded (the reference pushes
+// it with path_length max_px+1, astar.cpp:136, and aborts when it reaches the top of the heap,
+// astar.cpp:88-92).  The search stops after the first level k* that contains such a cell: every
+// target of a higher level is "None" because that heap entry has a smaller priority than any
+// goal of a higher level (65536 >> 2*max_px).  Targets settled at (k, j), k <= k*, get
 // path_length = k + j + 1 if that is <= max_px.
 //
-// Mapping to the SM: one CTA per source, persistent over a ticket counter.  The source's
-// window (L1 ball of radius max_px) is staged from the bit-packed frame mask in L2/HBM into
-// two shared-memory bitmaps in the folded-diamond layout of axb_common.cuh -- "open mask
-// pixel" and "open off-mask pixel"; claiming a cell is one shared-memory atomicAnd.  The
-// frontier lives in shared memory (global overflow for pathological masks); each wavefront is
-// expanded by four lanes per frontier cell and compacted with warp ballots.
+// Mapping to the SM.  A search is ~max_px dependent wavefronts of a few hundred cells: latency
+// bound, so the unit of work is ONE WARP per source and throughput comes from running
+// 3 x 148 independent searches at a time.
+//   k2_fast_kernel     level 0 only (the answer for every source whose mask component reaches
+//                      hop max_px or contains all its in-range targets -- all of them on real
+//                      data).  Window = one 64 KB "open mask pixel" bitmap in shared memory in the
+//                      folded-diamond layout of axb_common.cuh, staged with aligned 128 B row
+//                      reads of the bit-packed mask; claiming a cell is one shared-memory
+//                      atomicAnd; the frontier queue (shared, global overflow) is appended with
+//                      warp ballots, no counters in memory; targets are found through a 4 KB
+//                      shared hash of their window cells probed by the lane that claims a cell.
+//                      75 KB per CTA -> 3 CTAs (= 3 searches) per SM, persistent over a ticket.
+//   k2_general_kernel  all levels (second bitmap "open off-mask pixel", per-level seed lists in
+//                      global memory) for the sources the fast kernel defers: level 0 exhausted
+//                      below hop max_px with targets still open (source off the mask or in a
+//                      small component).
+//   k2_prep_kernel     chains, work prefix sums, counter reset (one CTA, tiny).
 #include "axb_common.cuh"
 
 namespace axb {
 
 namespace {
+
+constexpr unsigned kFull = 0xFFFFFFFFu;
 
 __device__ __forceinline__ uint32_t span_mask(int a, int b) {
     // bits i in [a, b] clipped to [0, 31]
@@ -37,360 +52,483 @@ __device__ __forceinline__ uint32_t span_mask(int a, int b) {
     return (0xFFFFFFFFu >> (31 - b)) & (0xFFFFFFFFu << a);
 }
 
-// 32 mask bits of image row `row` starting at pixel x0 (any alignment, may start left of the
-// image or run past it: missing words read as 0).
-__device__ __forceinline__ uint32_t load_bits(const uint32_t* __restrict__ row, int Wp, int x0) {
-    const int wi = x0 >> 5;            // arithmetic shift: floor
-    const int sh = x0 & 31;
-    const uint32_t lo = (wi >= 0 && wi < Wp) ? __ldg(row + wi) : 0u;
-    const uint32_t hi = (sh != 0 && wi + 1 >= 0 && wi + 1 < Wp) ? __ldg(row + wi + 1) : 0u;
-    return __funnelshift_r(lo, hi, sh);
+__device__ __forceinline__ uint32_t lanemask_lt() {
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
 }
 
-__device__ __forceinline__ int fold_index(int dy, int dx, int RW) {
+// queue entry: (dy + 512) << 11 | (cx + 512); cx = x - (sx & ~31) in [-511, 542]
+__device__ __forceinline__ uint32_t pack_cell(int dy, int cx) {
+    return ((uint32_t)(dy + 512) << 11) | (uint32_t)(cx + 512);
+}
+
+__device__ __forceinline__ int fold_index(int dy, int cx, int RW) {
     const int row = dy <= 0 ? dy + RW : dy - 1;
-    const int col = (dx + (dy <= 0 ? 512 : 0)) & (kRowBits - 1);
+    const int col = (cx + (dy <= 0 ? 512 : 0)) & (kRowBits - 1);
     return row * kRowBits + col;
 }
 
-__device__ __forceinline__ uint32_t pack_cell(int dy, int dx) {
-    return ((uint32_t)(dy + 512) << 10) | (uint32_t)(dx + 512);
+__device__ __forceinline__ uint32_t hash_slot(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
+static_assert(kHashSize == 1024, "hash_slot keeps 10 bits");
+static_assert(kCandCap <= 8192, "hash entries keep 13 bits of candidate slot");
+
+struct Src {
+    const uint32_t* mbits;
+    int H, W, Wp, sy, sx, iw0, o, RW;
+};
+
+// OR the bits of packed-mask word iw of image row y, restricted to x in [xlo, xhi], into fg/bg
+__device__ __forceinline__ void gather(const Src& s, int y, int iw, int xlo, int xhi, uint32_t& fg, uint32_t& bg) {
+    if (iw < 0 || iw >= s.Wp) return;
+    const uint32_t valid = span_mask(xlo - 32 * iw, xhi - 32 * iw);
+    if (!valid) return;
+    const uint32_t m = __ldg(s.mbits + (size_t)y * s.Wp + iw);
+    fg |= m & valid;
+    bg |= ~m & valid;
+}
+
+// Stage the folded window: lane = word of the folded row.  One shared word is one aligned word
+// of the packed mask: the upper half (dy <= 0) of folded row r sits at columns cx+512, the
+// lower half (dy = r+1) at columns cx (mod 1024); only lane 0 / lane 16 can see a second,
+// wrapped word of the same half.
+template <bool GEN>
+__device__ __forceinline__ void stage_window(const Src& s, uint32_t* OF, uint32_t* OB, int lane) {
+    const int RW = s.RW;
+    #pragma unroll 4
+    for (int r = 0; r <= RW; ++r) {
+        uint32_t fg = 0, bg = 0;
+        {
+            const int y = s.sy + r - RW;                       // upper half, half width r
+            if (y >= 0 && y < s.H) {
+                const int xlo = max(0, s.sx - r), xhi = min(s.W - 1, s.sx + r);
+                gather(s, y, s.iw0 - 16 + lane, xlo, xhi, fg, bg);
+                if (lane == 0) gather(s, y, s.iw0 + 16, xlo, xhi, fg, bg);
+            }
+        }
+        if (r + 1 <= RW) {
+            const int y = s.sy + r + 1;                        // lower half, half width RW-r-1
+            if (y >= 0 && y < s.H) {
+                const int hw = RW - r - 1;
+                const int xlo = max(0, s.sx - hw), xhi = min(s.W - 1, s.sx + hw);
+                gather(s, y, s.iw0 + (lane < 16 ? lane : lane - 32), xlo, xhi, fg, bg);
+                if (lane == 16) gather(s, y, s.iw0 + 16, xlo, xhi, fg, bg);
+            }
+        }
+        OF[r * kRowWords + lane] = fg;
+        if (GEN) OB[r * kRowWords + lane] = bg;
+    }
+}
+
+struct Chain {
+    long long orow[kMaxChain];      // first output element of this source's row, per member pair
+    long long item_orig[kMaxChain]; // work index in the reference's iteration order (errors)
+    int dst_off[kMaxChain];
+    int cum[kMaxChain + 1];         // flattened target index space
+    int nm;
+};
+
+// a target cell was reached at level k with j mask pixels on the path: hop = k + j
+__device__ __forceinline__ int probe_settle(const K2Params& p, const uint32_t* hash, const uint32_t* cand,
+                                            const Chain& ch, uint32_t key, int k, int j) {
+    int n = 0;
+    uint32_t h = hash_slot(key);
+    for (;;) {
+        const uint32_t e = hash[h];
+        if (e == kEmpty) break;
+        if ((e >> 13) == key) {
+            const uint32_t c = cand[e & 0x1FFFu];
+            const long long o = ch.orow[c >> 30] + (long long)(c & 0x3FFFFFFFu);
+            p.path_len[o] = k + j + 1;
+            p.unreachable[o] = 0;
+            if (p.wcost) p.wcost[o] = (float)(k * 65536 + j);
+            ++n;
+        }
+        h = (h + 1) & (kHashSize - 1);
+    }
+    return n;
+}
+
+// One work item = one source of a chain leader.  Returns true when the item must be redone by
+// the general kernel (fast kernel only).
+template <bool GEN>
+__device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Chain& ch) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = lanemask_lt();
+    const int RW = p.max_px;
+    const int nwords = (RW + 1) * kRowWords;
+    constexpr int QCAP = GEN ? kGenQCap : kFastQCap;
+    constexpr int GQCAP = GEN ? kGCap : kFastGQCap;
+
+    uint32_t* const OF = smem;
+    uint32_t* const OB = OF + (GEN ? nwords : 0);
+    uint32_t* const q0 = OB + nwords;
+    uint32_t* const hash = q0 + 2 * QCAP;
+    uint32_t* const cand = gscr;
+    uint32_t* const gq0 = gscr + kCandCap;
+    uint32_t* const gs0 = gq0 + 2 * (size_t)GQCAP;       // general only
+
+    // ---- which chain / source -------------------------------------------------------------
+    int lo = 0, hi = p.n_pairs - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (p.work_prefix[mid] <= item) lo = mid; else hi = mid - 1;
+    }
+    const int si = item - p.work_prefix[lo];
+    const axb_pair_desc lead = p.pairs[lo];
+    __syncwarp();
+    if (lane == 0) {
+        int q = lo, nm = 0;
+        ch.cum[0] = 0;
+        while (q >= 0 && nm < kMaxChain) {
+            const axb_pair_desc pd = p.pairs[q];
+            ch.orow[nm] = pd.out_off + (long long)si * pd.n_dst;
+            ch.item_orig[nm] = (long long)p.all_prefix[q] + si;
+            ch.dst_off[nm] = pd.dst_off;
+            ch.cum[nm + 1] = ch.cum[nm] + max(pd.n_dst, 0);
+            ++nm;
+            q = p.next_same[q];
+        }
+        ch.nm = nm;
+    }
+    __syncwarp();
+    const int nm = ch.nm;
+    const int total_t = ch.cum[nm];
+    if (total_t <= 0) return false;
+
+    Src s;
+    s.sy = p.dets_yx[2 * ((size_t)lead.src_off + si)];
+    s.sx = p.dets_yx[2 * ((size_t)lead.src_off + si) + 1];
+    s.H = p.H; s.W = p.W; s.Wp = p.Wp; s.RW = RW;
+    s.mbits = p.mask_bits + (size_t)lead.mask_idx * p.H * p.Wp;
+    s.iw0 = s.sx >> 5;                 // arithmetic shift; only used when the source is in the grid
+    s.o = s.sx & 31;
+    const bool src_in = s.sy >= 0 && s.sy < p.H && s.sx >= 0 && s.sx < p.W;
+    const long long r2 = (long long)RW * RW;
+    const int o = s.o;
+
+    int tt = 0;                        // next target of the flattened chain target list
+    for (;;) {                         // passes of <= kHashMaxLoad candidates (one on real data)
+        for (int i = lane; i < kHashSize; i += 32) hash[i] = kEmpty;
+        __syncwarp();
+        int ncand = 0;
+        while (tt < total_t) {
+            const int t = tt + lane;
+            bool is_cand = false, self = false, have = t < total_t;
+            int m = 0, j = 0, dy = 0, dx = 0;
+            if (have) {
+                while (m + 1 < nm && t >= ch.cum[m + 1]) ++m;
+                j = t - ch.cum[m];
+                const int ty = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j)];
+                const int tx = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j) + 1];
+                dy = ty - s.sy; dx = tx - s.sx;
+                const long long d2 = (long long)dy * dy + (long long)dx * dx;
+                if (d2 < r2) {                                        // AxonDetections.py:620-623
+                    const bool t_in = ty >= 0 && ty < p.H && tx >= 0 && tx < p.W;
+                    const unsigned long long ek = ((unsigned long long)ch.item_orig[m] << 26) | ((unsigned long long)j << 2);
+                    if (!src_in) atomicMin(p.err_key, ek | 1ull);     // astar_wrapper.py:39-42
+                    else if (!t_in) atomicMin(p.err_key, ek | 2ull);  // astar_wrapper.py:43-45
+                    else if (dy == 0 && dx == 0) self = true;         // start == goal: L = 1 (astar.cpp:67,99)
+                    else is_cand = abs(dy) + abs(dx) < RW;            // farther cells need > max_px pixels
+                }
+            }
+            const uint32_t bal = __ballot_sync(kFull, is_cand);
+            const int nb = __popc(bal);
+            if (ncand + nb > kHashMaxLoad) break;                     // next pass starts with this group
+            if (have) {
+                const long long oo = ch.orow[m] + j;
+                p.path_len[oo] = self ? 1 : RW;                       // None -> max_px (AxonDetections.py:736)
+                p.unreachable[oo] = self ? 0 : 1;
+                if (p.wcost) p.wcost[oo] = self ? 0.f : __int_as_float(0x7f800000);
+            }
+            if (is_cand) {
+                const uint32_t slot = (uint32_t)ncand + __popc(bal & lt);
+                cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
+                const uint32_t entry = ((uint32_t)fold_index(dy, dx + o, RW) << 13) | slot;
+                uint32_t h = hash_slot(entry >> 13);
+                while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (kHashSize - 1);
+            }
+            ncand += nb;
+            tt += 32;
+        }
+        __syncwarp();
+
+        if (ncand > 0) {
+            stage_window<GEN>(s, OF, OB, lane);
+            __syncwarp();
+            if (lane == 0) {       // close the source cell, seed the search with it
+                const int c = fold_index(0, o, RW);
+                OF[c >> 5] &= ~(1u << (c & 31));
+                if (GEN) OB[c >> 5] &= ~(1u << (c & 31));
+                q0[0] = pack_cell(0, o);
+                if (GEN) gs0[0] = pack_cell(0, o);      // tag j = 0
+            }
+            __syncwarp();
+
+            int unsettled = ncand;
+            uint32_t* qcur = q0;       uint32_t* qnxt = q0 + QCAP;
+            uint32_t* gcur = gq0;      uint32_t* gnxt = gq0 + GQCAP;
+
+            if (!GEN) {
+                // ---- level 0 only ---------------------------------------------------------
+                int cur_n = 1, j = 0;
+                bool hit = false, overflow = false;
+                while (cur_n > 0 && unsettled > 0) {
+                    if (j >= RW) { hit = true; break; }       // cells at hop == max_px exist
+                    int nxt_n = 0, my_set = 0;
+                    for (int base = 0; base < cur_n; base += 32) {
+                        const int i = base + lane;
+                        const bool act = i < cur_n;
+                        uint32_t e = 0;
+                        if (act) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
+                        const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
+                        #pragma unroll
+                        for (int d = 0; d < 4; ++d) {
+                            const int ndy = dy + (d == 0 ? -1 : d == 3 ? 1 : 0);
+                            const int ncx = cx + (d == 1 ? -1 : d == 2 ? 1 : 0);
+                            bool claimed = false;
+                            int idx = 0;
+                            if (act && abs(ndy) + abs(ncx - o) <= RW) {
+                                idx = fold_index(ndy, ncx, RW);
+                                const uint32_t bit = 1u << (idx & 31);
+                                if (OF[idx >> 5] & bit) claimed = (atomicAnd(&OF[idx >> 5], ~bit) & bit) != 0;
+                            }
+                            const uint32_t bal = __ballot_sync(kFull, claimed);
+                            if (bal) {
+                                if (claimed) {
+                                    const int slot = nxt_n + __popc(bal & lt);
+                                    const uint32_t ne = pack_cell(ndy, ncx);
+                                    if (slot < QCAP) qnxt[slot] = ne;
+                                    else if (slot - QCAP < GQCAP) gnxt[slot - QCAP] = ne;
+                                    if (j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx, 0, j + 1);
+                                }
+                                nxt_n += __popc(bal);
+                            }
+                        }
+                    }
+                    if (nxt_n > QCAP + GQCAP) { overflow = true; break; }
+                    unsettled -= __reduce_add_sync(kFull, my_set);
+                    __syncwarp();
+                    uint32_t* tq = qcur; qcur = qnxt; qnxt = tq;
+                    uint32_t* tg = gcur; gcur = gnxt; gnxt = tg;
+                    cur_n = nxt_n;
+                    ++j;
+                }
+                if (overflow || (!hit && unsettled > 0)) return true;     // level 0 cannot answer: defer
+            } else {
+                // ---- all levels -------------------------------------------------------------
+                uint32_t* gs_cur = gs0;   uint32_t* gs_nxt = gs0 + GQCAP;
+                int n_seeds = 1;
+                for (int k = 0; k <= RW && n_seeds > 0 && unsettled > 0; ++k) {
+                    int sp = 0, n_next = 0, cur_n = 0;
+                    int j = (int)(gs_cur[0] >> 21);
+                    bool hit = false;
+                    for (;;) {
+                        int ns = 0;                  // seeds tagged j (the list is sorted by tag)
+                        for (int pos = sp; pos < n_seeds; pos += 32) {
+                            const int i = pos + lane;
+                            const bool match = i < n_seeds && (int)(gs_cur[i] >> 21) == j;
+                            const int c = __popc(__ballot_sync(kFull, match));
+                            ns += c;
+                            if (c < 32) break;
+                        }
+                        if (cur_n + ns == 0) {
+                            if (sp >= n_seeds) break;              // level exhausted
+                            j = (int)(gs_cur[sp] >> 21);
+                            continue;
+                        }
+                        if (k + j >= RW) { hit = true; break; }     // cells at hop == max_px exist
+                        if (unsettled <= 0) break;
+                        const int tot = cur_n + ns;
+                        int nxt_n = 0, my_set = 0;
+                        for (int base = 0; base < tot; base += 32) {
+                            const int i = base + lane;
+                            const bool act = i < tot;
+                            uint32_t e = 0;
+                            bool seed = false;
+                            if (act) {
+                                if (i < cur_n) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
+                                else { e = gs_cur[sp + (i - cur_n)] & 0x1FFFFFu; seed = true; }
+                            }
+                            const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
+                            // off-mask cells settle when their level starts consuming them: by then
+                            // no lower level has reached hop max_px
+                            if (seed && k > 0) my_set += probe_settle(p, hash, cand, ch, (uint32_t)fold_index(dy, cx, RW), k, j);
+                            #pragma unroll
+                            for (int d = 0; d < 4; ++d) {
+                                const int ndy = dy + (d == 0 ? -1 : d == 3 ? 1 : 0);
+                                const int ncx = cx + (d == 1 ? -1 : d == 2 ? 1 : 0);
+                                bool got_fg = false, got_bg = false;
+                                int idx = 0;
+                                if (act && abs(ndy) + abs(ncx - o) <= RW) {
+                                    idx = fold_index(ndy, ncx, RW);
+                                    const uint32_t bit = 1u << (idx & 31);
+                                    if (OF[idx >> 5] & bit) got_fg = (atomicAnd(&OF[idx >> 5], ~bit) & bit) != 0;
+                                    else if (OB[idx >> 5] & bit) got_bg = (atomicAnd(&OB[idx >> 5], ~bit) & bit) != 0;
+                                }
+                                const uint32_t bf = __ballot_sync(kFull, got_fg);
+                                const uint32_t bb = __ballot_sync(kFull, got_bg);
+                                if (bf) {
+                                    if (got_fg) {
+                                        const int slot = nxt_n + __popc(bf & lt);
+                                        const uint32_t ne = pack_cell(ndy, ncx);
+                                        if (slot < QCAP) qnxt[slot] = ne; else gnxt[slot - QCAP] = ne;
+                                        if (k + j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx, k, j + 1);
+                                    }
+                                    nxt_n += __popc(bf);
+                                }
+                                if (bb) {
+                                    if (got_bg) gs_nxt[n_next + __popc(bb & lt)] = ((uint32_t)j << 21) | pack_cell(ndy, ncx);
+                                    n_next += __popc(bb);
+                                }
+                            }
+                        }
+                        unsettled -= __reduce_add_sync(kFull, my_set);
+                        __syncwarp();
+                        uint32_t* tq = qcur; qcur = qnxt; qnxt = tq;
+                        uint32_t* tg = gcur; gcur = gnxt; gnxt = tg;
+                        sp += ns;
+                        cur_n = nxt_n;
+                        ++j;
+                    }
+                    if (hit) break;                    // k* = k: every deeper target stays None
+                    uint32_t* ts = gs_cur; gs_cur = gs_nxt; gs_nxt = ts;
+                    n_seeds = n_next;
+                    __syncwarp();
+                }
+            }
+        }
+        if (tt >= total_t) break;
+    }
+    return false;
 }
 
 }  // namespace
 
-template <int NT>
-__global__ void __launch_bounds__(NT, 1) k2_search_kernel(const K2Params p) {
+__global__ void __launch_bounds__(32, kFastCtasPerSm) k2_fast_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
-    const int tid = threadIdx.x;
-    const int lane = tid & 31;
-    const int RW = p.max_px;
-    const int nrows = RW + 1;
-    const int nwords = nrows * kRowWords;
-
-    uint32_t* const OF = smem;                 // open mask pixels      [nrows][32]
-    uint32_t* const OB = OF + nwords;          // open off-mask pixels  [nrows][32]
-    uint32_t* const q0 = OB + nwords;          // frontier buffers      [2][kQCap]
-    uint32_t* const send0 = q0 + 2 * kQCap;    // seed calendars        [2][kSeedEnd]
-    uint32_t* const tcell = send0 + 2 * kSeedEnd;   // in-range targets: bit31 = on mask, low = fold index
-    uint32_t* const tidx = tcell + kTCap;           // target index j
-    uint32_t* const tres = tidx + kTCap;            // (k << 16 | j) once settled
-
-    __shared__ uint32_t s_cnt[3];
-    __shared__ uint32_t s_seedcnt;
-    __shared__ uint32_t s_ntgt;
-    __shared__ int s_item;
-
-    uint32_t* const gq0 = p.scratch + (size_t)blockIdx.x * 4 * kGCap;   // frontier overflow [2][kGCap]
-    uint32_t* const gs0 = gq0 + 2 * kGCap;                              // seeds            [2][kGCap]
-
-    const long long r2 = (long long)p.max_px * p.max_px;
-
+    __shared__ Chain ch;
+    uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
+    const int total = p.work_prefix[p.n_pairs];
     for (;;) {
-        __syncthreads();
-        if (tid == 0) s_item = atomicAdd(p.work_counter, 1);
-        __syncthreads();
-        const int item = s_item;
-        if (item >= p.work_prefix[p.n_pairs]) break;
-
-        // ---- which pair / source ------------------------------------------------------
-        // work_prefix = exclusive prefix of n_src over the pairs (launch_work_prefix)
-        int lo = 0, hi = p.n_pairs - 1;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (p.work_prefix[mid] <= item) lo = mid; else hi = mid - 1;
-        }
-        const axb_pair_desc pd = p.pairs[lo];
-        const int si = item - p.work_prefix[lo];
-        const int n_dst = pd.n_dst;
-        if (n_dst <= 0) continue;
-        const int sy = p.dets_yx[2 * (pd.src_off + si)];
-        const int sx = p.dets_yx[2 * (pd.src_off + si) + 1];
-        const bool src_in = sy >= 0 && sy < p.H && sx >= 0 && sx < p.W;
-        const int32_t* __restrict__ dst = p.dets_yx + 2 * (size_t)pd.dst_off;
-        const uint32_t* __restrict__ mbits = p.mask_bits + (size_t)pd.mask_idx * p.H * p.Wp;
-        const long long orow = pd.out_off + (long long)si * n_dst;
-
-        for (int tb = 0; tb < n_dst; tb += kTCap) {
-            const int tend = min(n_dst, tb + kTCap);
-            __syncthreads();
-            if (tid == 0) s_ntgt = 0;
-            __syncthreads();
-
-            // ---- defaults + in-range target list -----------------------------------------
-            for (int j0 = tb; j0 < tend; j0 += NT) {
-                const int j = j0 + tid;
-                bool listed = false;
-                int dy = 0, dx = 0;
-                if (j < tend) {
-                    p.path_len[orow + j] = p.max_px;
-                    p.unreachable[orow + j] = 1;
-                    if (p.wcost) p.wcost[orow + j] = __int_as_float(0x7f800000);
-                    const int ty = dst[2 * j], tx = dst[2 * j + 1];
-                    dy = ty - sy; dx = tx - sx;
-                    const long long d2 = (long long)dy * dy + (long long)dx * dx;
-                    if (d2 < r2) {                                   // AxonDetections.py:620-623
-                        const bool t_in = ty >= 0 && ty < p.H && tx >= 0 && tx < p.W;
-                        if (!src_in)
-                            atomicMin(p.err_key, ((unsigned long long)item << 26) | ((unsigned long long)j << 2) | 1ull);
-                        else if (!t_in)
-                            atomicMin(p.err_key, ((unsigned long long)item << 26) | ((unsigned long long)j << 2) | 2ull);
-                        else
-                            listed = (abs(dy) + abs(dx) < RW);       // farther cells cannot be reached in < max_px hops
-                    }
-                }
-                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, listed);
-                if (bal) {
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&s_ntgt, __popc(bal));
-                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                    if (listed) {
-                        const uint32_t slot = base + __popc(bal & ((1u << lane) - 1));
-                        tcell[slot] = (uint32_t)fold_index(dy, dx, RW);
-                        tidx[slot] = (uint32_t)j;
-                        tres[slot] = (dy == 0 && dx == 0) ? 0u : kUnset;   // target == source: (k, j) = (0, 0)
-                    }
-                }
-            }
-            __syncthreads();
-            const int ntgt = (int)s_ntgt;
-            if (ntgt == 0) continue;      // uniform: nothing in range (or input error) -> all None
-
-            // ---- stage the window ---------------------------------------------------------
-            for (int i = tid; i < nwords; i += NT) {
-                const int r = i >> 5, w = i & 31;
-                uint32_t fg = 0, bg = 0;
-                {   // own half: dy = r - RW <= 0, centred at column 512
-                    const int y = sy + r - RW;
-                    const int hw = r;                    // RW - |dy|
-                    const int x0 = sx + 32 * w - 512;    // pixel of bit 0
-                    uint32_t valid = span_mask(512 - hw - 32 * w, 512 + hw - 32 * w) &
-                                     span_mask(-x0, p.W - 1 - x0);
-                    if (y < 0 || y >= p.H) valid = 0;
-                    if (valid) {
-                        const uint32_t m = load_bits(mbits + (size_t)y * p.Wp, p.Wp, x0);
-                        fg |= m & valid; bg |= ~m & valid;
-                    }
-                }
-                if (r + 1 <= RW) {   // partner half: dy = r + 1 > 0, centred at column 0 (mod 1024)
-                    const int y = sy + r + 1;
-                    const int hw = RW - r - 1;
-                    const int off = w < 16 ? 0 : 1024;
-                    const int x0 = sx + 32 * w - off;
-                    uint32_t valid = span_mask(off - hw - 32 * w, off + hw - 32 * w) &
-                                     span_mask(-x0, p.W - 1 - x0);
-                    if (y < 0 || y >= p.H) valid = 0;
-                    if (valid) {
-                        const uint32_t m = load_bits(mbits + (size_t)y * p.Wp, p.Wp, x0);
-                        fg |= m & valid; bg |= ~m & valid;
-                    }
-                }
-                OF[i] = fg;
-                OB[i] = bg;
-            }
-            __syncthreads();
-
-            // ---- classify targets (on / off mask), then close the source cell --------------
-            for (int t = tid; t < ntgt; t += NT) {
-                const uint32_t c = tcell[t];
-                if (OF[c >> 5] & (1u << (c & 31))) tcell[t] = c | 0x80000000u;
-            }
-            __syncthreads();
-            if (tid == 0) {
-                const int c = fold_index(0, 0, RW);
-                OF[c >> 5] &= ~(1u << (c & 31));
-                OB[c >> 5] &= ~(1u << (c & 31));
-                gs0[0] = pack_cell(0, 0);                 // level 0 is seeded by the source at j = 0
-            }
-            for (int j = tid; j < kSeedEnd; j += NT) send0[j] = 1u;
-            __syncthreads();
-
-            // ---- levels ---------------------------------------------------------------------
-            int kstar = -1;
-            bool my_pending = false;               // does this thread still own an unsettled target?
-            for (int t = tid; t < ntgt; t += NT) my_pending |= (tres[t] == kUnset);
-            bool all_settled = false;
-            uint32_t seeds_total = 1;
-            int sb = 0;
-            int jscan = 0;
-            for (int k = 0; k <= RW && seeds_total > 0 && !all_settled; ++k) {
-                const uint32_t* const send_cur = send0 + sb * kSeedEnd;
-                uint32_t* const send_nxt = send0 + (sb ^ 1) * kSeedEnd;
-                const uint32_t* const gs_cur = gs0 + (size_t)sb * kGCap;
-                uint32_t* const gs_nxt = gs0 + (size_t)(sb ^ 1) * kGCap;
-                if (tid == 0) { s_seedcnt = 0; s_cnt[0] = 0; s_cnt[1] = 0; s_cnt[2] = 0; }
-                int j = jscan;
-                while (send_cur[j] == 0) ++j;          // first seeded j of this level
-                jscan = j;
-                uint32_t sp = 0;                       // seeds consumed
-                uint32_t nlist = 0;                    // mask pixels claimed by the previous wave
-                int step = 0;
-                bool hit = false;
-                __syncthreads();
-                for (;;) {
-                    const uint32_t send = send_cur[j];
-                    const uint32_t ncur = nlist + (send - sp);
-                    if (ncur == 0) {
-                        if (sp >= seeds_total) break;          // level exhausted
-                        if (tid == 0) send_nxt[j] = s_seedcnt;
-                        ++j;
-                        continue;
-                    }
-                    if (k + j >= RW) { hit = true; break; }    // cells at hop == max_px exist
-
-                    const uint32_t* const qcur = q0 + (step & 1) * kQCap;
-                    const uint32_t* const gqcur = gq0 + (size_t)(step & 1) * kGCap;
-                    uint32_t* const qnxt = q0 + ((step + 1) & 1) * kQCap;
-                    uint32_t* const gqnxt = gq0 + (size_t)((step + 1) & 1) * kGCap;
-                    uint32_t* const cnt_nxt = &s_cnt[(step + 1) % 3];
-
-                    const uint32_t ntask = ncur * 4;
-                    for (uint32_t t0 = 0; t0 < ntask; t0 += NT) {
-                        const uint32_t task = t0 + tid;
-                        bool got_fg = false, got_bg = false;
-                        uint32_t ncell = 0;
-                        if (task < ntask) {
-                            const uint32_t ci = task >> 2;
-                            uint32_t e;
-                            if (ci < nlist) e = ci < (uint32_t)kQCap ? qcur[ci] : gqcur[ci - kQCap];
-                            else            e = gs_cur[sp + (ci - nlist)];
-                            int dy = (int)((e >> 10) & 1023u) - 512;
-                            int dx = (int)(e & 1023u) - 512;
-                            const int dir = task & 3;
-                            dy += (dir == 0) ? -1 : (dir == 3) ? 1 : 0;
-                            dx += (dir == 1) ? -1 : (dir == 2) ? 1 : 0;
-                            if (abs(dy) + abs(dx) <= RW) {
-                                const int c = fold_index(dy, dx, RW);
-                                const uint32_t bit = 1u << (c & 31);
-                                const int w = c >> 5;
-                                if (OF[w] & bit) {
-                                    got_fg = (atomicAnd(&OF[w], ~bit) & bit) != 0;
-                                } else if (OB[w] & bit) {
-                                    got_bg = (atomicAnd(&OB[w], ~bit) & bit) != 0;
-                                }
-                                ncell = pack_cell(dy, dx);
-                            }
-                        }
-                        const uint32_t bf = __ballot_sync(0xFFFFFFFFu, got_fg);
-                        const uint32_t bb = __ballot_sync(0xFFFFFFFFu, got_bg);
-                        if (bf) {
-                            uint32_t base = 0;
-                            if (lane == 0) base = atomicAdd(cnt_nxt, __popc(bf));
-                            base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                            if (got_fg) {
-                                const uint32_t slot = base + __popc(bf & ((1u << lane) - 1));
-                                if (slot < (uint32_t)kQCap) qnxt[slot] = ncell; else gqnxt[slot - kQCap] = ncell;
-                            }
-                        }
-                        if (bb) {
-                            uint32_t base = 0;
-                            if (lane == 0) base = atomicAdd(&s_seedcnt, __popc(bb));
-                            base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                            if (got_bg) gs_nxt[base + __popc(bb & ((1u << lane) - 1))] = ncell;
-                        }
-                    }
-                    // barrier + "is any target still unsettled" (as of the previous wave's poll);
-                    // once every in-range target is settled no later level can change the answer
-                    if (!__syncthreads_or(my_pending)) { all_settled = true; break; }
-                    nlist = *cnt_nxt;
-                    if (tid == 0) { s_cnt[step % 3] = 0; send_nxt[j] = s_seedcnt; }
-                    sp = send;
-                    // targets settled by this wave: mask pixels at (k, j+1), off-mask pixels at (k+1, j)
-                    my_pending = false;
-                    for (int t = tid; t < ntgt; t += NT) {
-                        if (tres[t] == kUnset) {
-                            const uint32_t c = tcell[t];
-                            const uint32_t ci = c & 0x7FFFFFFFu;
-                            const uint32_t bit = 1u << (ci & 31);
-                            if (c & 0x80000000u) {
-                                if (!(OF[ci >> 5] & bit)) tres[t] = ((uint32_t)k << 16) | (uint32_t)(j + 1);
-                                else my_pending = true;
-                            } else {
-                                if (!(OB[ci >> 5] & bit)) tres[t] = ((uint32_t)(k + 1) << 16) | (uint32_t)j;
-                                else my_pending = true;
-                            }
-                        }
-                    }
-                    ++j;
-                    ++step;
-                }
-                // ---- level end ------------------------------------------------------------
-                __syncthreads();
-                const uint32_t total_next = s_seedcnt;
-                for (int jj = tid; jj < kSeedEnd; jj += NT) {
-                    if (jj >= j) send_nxt[jj] = total_next;
-                    else if (jj < jscan) send_nxt[jj] = 0;
-                }
-                if (hit) kstar = k;
-                seeds_total = (hit || all_settled) ? 0 : total_next;
-                sb ^= 1;
-                __syncthreads();
-            }
-
-            // ---- resolve ----------------------------------------------------------------------
-            for (int t = tid; t < ntgt; t += NT) {
-                const uint32_t r = tres[t];
-                if (r == kUnset) continue;
-                const int kT = (int)(r >> 16), jT = (int)(r & 0xFFFFu);
-                if (kT + jT + 1 > p.max_px) continue;
-                if (kstar >= 0 && kT > kstar) continue;
-                const long long o = orow + tidx[t];
-                p.path_len[o] = kT + jT + 1;
-                p.unreachable[o] = 0;
-                if (p.wcost) p.wcost[o] = (float)kT * 65536.0f + (float)jT;
-            }
-        }
+        int item = 0;
+        if (threadIdx.x == 0) item = atomicAdd(&p.counters[0], 1);
+        item = __shfl_sync(kFull, item, 0);
+        if (item >= total) break;
+        const bool defer = run_item<false>(p, item, smem, gscr, ch);
+        if (defer && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+        __syncwarp();
     }
 }
 
-// work_prefix[i] = sum of n_src over pairs < i, work_prefix[n_pairs] = total (one CTA, tiny)
-__global__ void work_prefix_kernel(const axb_pair_desc* __restrict__ pairs, int n_pairs, int* __restrict__ prefix) {
-    __shared__ int s_carry;
-    __shared__ int s_warp[32];
-    if (threadIdx.x == 0) s_carry = 0;
+__global__ void __launch_bounds__(32, 1) k2_general_kernel(const K2Params p) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ Chain ch;
+    uint32_t* const gscr = p.gen_scratch + (size_t)blockIdx.x * kGenScratchWords;
+    const int total = p.counters[1];
+    for (;;) {
+        int t = 0;
+        if (threadIdx.x == 0) t = atomicAdd(&p.counters[2], 1);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= total) break;
+        run_item<true>(p, p.gen_list[t], smem, gscr, ch);
+        __syncwarp();
+    }
+}
+
+// Chains + prefix sums + counter reset, one CTA.
+//   same key = same (mask_idx, src_off, n_src): the searches of the two pairs are identical, only
+//   the targets differ.  prev/next link same-key pairs inside a +-kChainWindow index window; a
+//   pair whose depth in its list is a multiple of kMaxChain leads a chain of <= kMaxChain pairs.
+constexpr int kChainWindow = 16;
+__global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __restrict__ pairs, int n_pairs,
+                                                         int* __restrict__ work_prefix, int* __restrict__ all_prefix,
+                                                         int* __restrict__ next_same, int* __restrict__ counters) {
+    __shared__ int s_carry[2];
+    __shared__ int s_warp[2][32];
+    const int tid = threadIdx.x;
+    int* const prev = work_prefix;            // scratch until the scan overwrites it
+    if (tid < 3) counters[tid] = 0;
+    for (int i = tid; i < n_pairs; i += blockDim.x) {
+        const axb_pair_desc a = pairs[i];
+        int pv = -1, nx = -1;
+        if (a.n_src > 0) {
+            for (int q = i - 1; q >= max(0, i - kChainWindow); --q) {
+                const axb_pair_desc b = pairs[q];
+                if (b.mask_idx == a.mask_idx && b.src_off == a.src_off && b.n_src == a.n_src) { pv = q; break; }
+            }
+            for (int q = i + 1; q <= min(n_pairs - 1, i + kChainWindow); ++q) {
+                const axb_pair_desc b = pairs[q];
+                if (b.mask_idx == a.mask_idx && b.src_off == a.src_off && b.n_src == a.n_src) { nx = q; break; }
+            }
+        }
+        prev[i] = pv;
+        next_same[i] = nx;
+    }
+    __syncthreads();
+    // depth in the list -> leader flag, kept in all_prefix until the scan
+    for (int i = tid; i < n_pairs; i += blockDim.x) {
+        int d = 0;
+        for (int q = prev[i]; q >= 0; q = prev[q]) ++d;
+        all_prefix[i] = (d % kMaxChain) == 0;
+    }
+    __syncthreads();
+    if (tid == 0) { s_carry[0] = 0; s_carry[1] = 0; }
     __syncthreads();
     for (int base = 0; base < n_pairs; base += blockDim.x) {
-        const int i = base + threadIdx.x;
-        const int v = i < n_pairs ? max(pairs[i].n_src, 0) : 0;
-        int x = v;
+        const int i = base + tid;
+        const int na = i < n_pairs ? max(pairs[i].n_src, 0) : 0;
+        const int nw = (i < n_pairs && all_prefix[i]) ? na : 0;
+        int xa = na, xw = nw;
         for (int o = 1; o < 32; o <<= 1) {
-            const int y = __shfl_up_sync(0xFFFFFFFFu, x, o);
-            if ((threadIdx.x & 31) >= o) x += y;
+            const int ya = __shfl_up_sync(kFull, xa, o), yw = __shfl_up_sync(kFull, xw, o);
+            if ((tid & 31) >= o) { xa += ya; xw += yw; }
         }
-        if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = x;
+        if ((tid & 31) == 31) { s_warp[0][tid >> 5] = xa; s_warp[1][tid >> 5] = xw; }
         __syncthreads();
-        if (threadIdx.x < 32) {
-            int w = threadIdx.x < (blockDim.x >> 5) ? s_warp[threadIdx.x] : 0;
+        if (tid < 32) {
+            int wa = tid < (int)(blockDim.x >> 5) ? s_warp[0][tid] : 0;
+            int ww = tid < (int)(blockDim.x >> 5) ? s_warp[1][tid] : 0;
             for (int o = 1; o < 32; o <<= 1) {
-                const int y = __shfl_up_sync(0xFFFFFFFFu, w, o);
-                if (threadIdx.x >= o) w += y;
+                const int ya = __shfl_up_sync(kFull, wa, o), yw = __shfl_up_sync(kFull, ww, o);
+                if (tid >= o) { wa += ya; ww += yw; }
             }
-            s_warp[threadIdx.x] = w;
+            s_warp[0][tid] = wa; s_warp[1][tid] = ww;
         }
         __syncthreads();
-        const int warp_off = (threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0;
-        const int incl = s_carry + warp_off + x;
-        if (i < n_pairs) prefix[i] = incl - v;
+        const int offa = (tid >> 5) ? s_warp[0][(tid >> 5) - 1] : 0;
+        const int offw = (tid >> 5) ? s_warp[1][(tid >> 5) - 1] : 0;
+        const int incla = s_carry[0] + offa + xa, inclw = s_carry[1] + offw + xw;
         __syncthreads();
-        if (threadIdx.x == blockDim.x - 1) s_carry = incl;
+        if (i < n_pairs) { all_prefix[i] = incla - na; work_prefix[i] = inclw - nw; }
+        if (tid == (int)blockDim.x - 1) { s_carry[0] = incla; s_carry[1] = inclw; }
         __syncthreads();
     }
-    if (threadIdx.x == 0) prefix[n_pairs] = s_carry;
+    if (tid == 0) { all_prefix[n_pairs] = s_carry[0]; work_prefix[n_pairs] = s_carry[1]; }
 }
 
-void launch_k2(const K2Params& p, int grid, cudaStream_t stream) {
-    const size_t smem = k2_smem_bytes(p.max_px);
+void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
+                    int* next_same, int* counters, cudaStream_t stream) {
+    k2_prep_kernel<<<1, 1024, 0, stream>>>(pairs, n_pairs, work_prefix, all_prefix, next_same, counters);
+}
+
+void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(k2_search_kernel<kK2Threads>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)k2_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_fast_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr_set = true;
     }
-    k2_search_kernel<kK2Threads><<<grid, kK2Threads, smem, stream>>>(p);
+    k2_fast_kernel<<<grid, 32, k2_fast_smem_bytes(p.max_px), stream>>>(p);
 }
 
-void launch_work_prefix(const axb_pair_desc* pairs, int n_pairs, int* prefix, cudaStream_t stream) {
-    work_prefix_kernel<<<1, 256, 0, stream>>>(pairs, n_pairs, prefix);
+void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k2_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_gen_smem_bytes(AXB_MAX_PX));
+        attr_set = true;
+    }
+    k2_general_kernel<<<grid, 32, k2_gen_smem_bytes(p.max_px), stream>>>(p);
 }
 
 }  // namespace axb

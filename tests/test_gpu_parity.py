@@ -243,3 +243,68 @@ def test_full_size_properties(cuda):
     assert (np.diag(pls) == 1).all() and (np.diag(uns) == 0).all()
     rows = np.arange(0, len(a), 9)
     _check((pl[rows], un[rows], wc[rows]), oracle.cost_matrix_rule(mask, a[rows], b, 500))
+
+
+def test_many_targets_multi_pass(cuda):
+    """> kHashMaxLoad (640) in-range targets per source (several search passes), duplicate target
+    cells, targets equal to the source, open field (frontier spills to the global queue)."""
+    rng = np.random.default_rng(7)
+    H, W = 420, 380
+    m = np.ones((H, W), np.uint8)
+    m[100:300, 190] = 0                      # a wall with a detour
+    m[40, 20:200] = 0
+    src = np.stack([rng.integers(0, H, 5), rng.integers(0, W, 5)], 1).astype(np.int32)
+    dst = np.stack([rng.integers(0, H, 1500), rng.integers(0, W, 1500)], 1).astype(np.int32)
+    dst[10] = dst[11] = dst[12]              # duplicates
+    dst[20] = src[0]; dst[21] = src[3]       # start == goal
+    for max_px in (500, 90):
+        _check(_gpu_cost(cuda, m, src, dst, max_px), oracle.cost_matrix_rule(m, src, dst, max_px), max_px)
+
+
+def test_chain_sharing_and_batches(cuda):
+    """Pairs that share (mask, sources) are answered by one search; pairs that do not, are not.
+    Compared per pair with the oracle; includes per-frame masks and an empty frame."""
+    from axtrack_b200 import ops
+    rng = np.random.default_rng(3)
+    H, W = 300, 340
+    masks = np.stack([synth.make_mask(H, W, s, pitch=(40, 90), width=(4, 10)) for s in (1, 2)]).astype(np.uint8)
+    frames = [synth.make_tracks(masks[0].astype(bool), 25, 1, s, off_mask_frac=0.2)[0] for s in range(5)]
+    frames[3] = np.zeros((0, 2), np.int32)
+    offs = np.concatenate([[0], np.cumsum([len(f) for f in frames])])
+    dets = np.concatenate(frames).astype(np.int32)
+    # (mask, src frame, dst frame): 0-2 share a search (same mask + sources), 3 differs by mask,
+    # 4 has an empty target frame, 5 an empty source frame, 6-10 a chain longer than kMaxChain
+    spec = [(0, 0, 1), (0, 0, 2), (0, 0, 4), (1, 0, 1), (0, 1, 3), (0, 3, 1)] + [(1, 2, 4)] * 5
+    pairs, total, _ = ops.make_pairs([(mk, int(offs[a]), len(frames[a]), int(offs[b]), len(frames[b])) for mk, a, b in spec])
+    bits = ops.pack_mask(cuda.from_numpy(masks).cuda())
+    pl, un, wc, _ = ops.cost_matrix_batch(bits, W, cuda.from_numpy(dets).cuda(), pairs, 120)
+    ops.raise_status()
+    pl, un, wc = pl.cpu().numpy(), un.cpu().numpy(), wc.cpu().numpy()
+    for (mk, a, b), pd in zip(spec, pairs):
+        o, ns, nd = int(pd['out_off']), int(pd['n_src']), int(pd['n_dst'])
+        sl = slice(o, o + ns * nd)
+        ref = oracle.cost_matrix_rule(masks[mk], frames[a], frames[b], 120)
+        _check((pl[sl].reshape(ns, nd), un[sl].reshape(ns, nd), wc[sl].reshape(ns, nd)),
+               (ref[0].reshape(ns, nd), ref[1].reshape(ns, nd), ref[2].reshape(ns, nd)), (mk, a, b))
+
+
+def test_general_path_sources(cuda):
+    """Sources off the mask / in small components (deferred to the all-levels kernel) at
+    max_px = 500 on a corridor mask; vs the closed form and, on a sample, the per-pair A*."""
+    H, W = 700, 900
+    mask = synth.make_mask(H, W, 9, pitch=(80, 170), width=(5, 12))
+    mask[300:306, 400:420] = True            # an island
+    mask[296:300, :] &= False
+    rng = np.random.default_rng(9)
+    fg = np.argwhere(mask)
+    src = fg[rng.integers(0, len(fg), 24)] + rng.integers(-6, 7, (24, 2))
+    src = np.vstack([src, [[302, 405], [303, 418]]])
+    dst = fg[rng.integers(0, len(fg), 60)] + rng.integers(-3, 4, (60, 2)) * (rng.random((60, 1)) < 0.4)
+    for a in (src, dst):
+        a[:, 0] = np.clip(a[:, 0], 0, H - 1); a[:, 1] = np.clip(a[:, 1], 0, W - 1)
+    src, dst = src.astype(np.int32), dst.astype(np.int32)
+    got = _gpu_cost(cuda, mask, src, dst, 500)
+    _check(got, oracle.cost_matrix_rule(mask, src, dst, 500))
+    sub = np.arange(0, len(src), 5)
+    a = oracle.cost_matrix_astar(mask, src[sub], dst, 500)
+    assert np.array_equal(got[0][sub], a[0]) and np.array_equal(got[1][sub], a[1])
