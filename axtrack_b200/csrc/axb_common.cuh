@@ -22,11 +22,13 @@ constexpr int kMaxChain = 4;          // frame pairs that share one source searc
 constexpr int kHashSize = 1024;       // target-cell hash (u32 entries) in shared memory
 constexpr int kHashMaxLoad = 640;     // candidates per search pass
 constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
-// fast kernel (level 0 only): one warp per source, 3 CTAs per SM
+constexpr int kK2Threads = 128;       // one CTA (4 warps) per source search
+constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
+// fast kernel (level 0 only): 3 CTAs per SM
 constexpr int kFastQCap = 768;        // frontier entries per buffer in shared memory
 constexpr int kFastGQCap = 16384;     // per-CTA global overflow entries per buffer
 constexpr int kFastCtasPerSm = 3;
-// general kernel (all levels): one warp per source, both bitmaps, 1 CTA per SM
+// general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;
@@ -55,7 +57,7 @@ inline size_t k2_fast_smem_bytes(int max_px) {
     return ((size_t)(max_px + 1) * kRowWords + 2 * kFastQCap + kHashSize) * sizeof(uint32_t);
 }
 inline size_t k2_gen_smem_bytes(int max_px) {
-    return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize) * sizeof(uint32_t);
+    return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
 }
 constexpr size_t kFastScratchWords = (size_t)kCandCap + 2 * (size_t)kFastGQCap;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;

@@ -20,21 +20,23 @@
 // path_length = k + j + 1 if that is <= max_px.
 //
 // Mapping to the SM.  A search is ~max_px dependent wavefronts of a few hundred cells: latency
-// bound, so the unit of work is ONE WARP per source and throughput comes from running
-// 3 x 148 independent searches at a time.
+// bound.  One CTA of kK2Threads (4 warps) per source, one __syncthreads per wavefront, and
+// throughput from 3 resident CTAs per SM x 148 SMs of independent searches.
 //   k2_fast_kernel     level 0 only (the answer for every source whose mask component reaches
-//                      hop max_px or contains all its in-range targets -- all of them on real
-//                      data).  Window = one 64 KB "open mask pixel" bitmap in shared memory in the
-//                      folded-diamond layout of axb_common.cuh, staged with aligned 128 B row
-//                      reads of the bit-packed mask; claiming a cell is one shared-memory
-//                      atomicAnd; the frontier queue (shared, global overflow) is appended with
-//                      warp ballots, no counters in memory; targets are found through a 4 KB
-//                      shared hash of their window cells probed by the lane that claims a cell.
-//                      75 KB per CTA -> 3 CTAs (= 3 searches) per SM, persistent over a ticket.
+//                      hop max_px or contains all its in-range targets -- nearly all of them on
+//                      real data).  Window = one 64 KB "open mask pixel" bitmap in shared memory
+//                      in the folded-diamond layout of axb_common.cuh (rows rotated by their index
+//                      so that a vertical run of cells spreads over the 32 banks), staged with
+//                      aligned 128 B row reads of the bit-packed mask; claiming a cell is one
+//                      shared-memory atomicAnd; the frontier queue (shared, global overflow) is
+//                      appended with one warp-aggregated atomicAdd per 32 cells; targets are
+//                      found through a 4 KB shared hash of their window cells probed by the lane
+//                      that claims a cell.  75 KB per CTA -> 3 CTAs per SM, persistent over a
+//                      ticket counter.
 //   k2_general_kernel  all levels (second bitmap "open off-mask pixel", per-level seed lists in
-//                      global memory) for the sources the fast kernel defers: level 0 exhausted
-//                      below hop max_px with targets still open (source off the mask or in a
-//                      small component).
+//                      global memory with a per-j calendar in shared memory) for the sources the
+//                      fast kernel defers: level 0 exhausted below hop max_px with targets still
+//                      open (source off the mask or in a small component).
 //   k2_prep_kernel     chains, work prefix sums, counter reset (one CTA, tiny).
 #include "axb_common.cuh"
 
@@ -63,10 +65,17 @@ __device__ __forceinline__ uint32_t pack_cell(int dy, int cx) {
     return ((uint32_t)(dy + 512) << 11) | (uint32_t)(cx + 512);
 }
 
+// logical cell index of the folded window: row * 1024 + column (the hash key of a target)
 __device__ __forceinline__ int fold_index(int dy, int cx, int RW) {
     const int row = dy <= 0 ? dy + RW : dy - 1;
     const int col = (cx + (dy <= 0 ? 512 : 0)) & (kRowBits - 1);
     return row * kRowBits + col;
+}
+
+// shared-memory word of a logical cell index: the 32 words of row r are rotated by r
+__device__ __forceinline__ int phys_word(int idx) {
+    const int row = idx >> 10;
+    return (row << 5) | (((idx >> 5) + row) & 31);
 }
 
 __device__ __forceinline__ uint32_t hash_slot(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
@@ -88,15 +97,16 @@ __device__ __forceinline__ void gather(const Src& s, int y, int iw, int xlo, int
     bg |= ~m & valid;
 }
 
-// Stage the folded window: lane = word of the folded row.  One shared word is one aligned word
-// of the packed mask: the upper half (dy <= 0) of folded row r sits at columns cx+512, the
-// lower half (dy = r+1) at columns cx (mod 1024); only lane 0 / lane 16 can see a second,
-// wrapped word of the same half.
-template <bool GEN>
-__device__ __forceinline__ void stage_window(const Src& s, uint32_t* OF, uint32_t* OB, int lane) {
+// Stage the folded window: one warp per folded row, lane = logical word of the row.  One shared
+// word is one aligned word of the packed mask: the upper half (dy <= 0) of folded row r sits at
+// columns cx+512, the lower half (dy = r+1) at columns cx (mod 1024); only lane 0 / lane 16 can
+// see a second, wrapped word of the same half.
+template <bool GEN, int NT>
+__device__ __forceinline__ void stage_window(const Src& s, uint32_t* OF, uint32_t* OB) {
     const int RW = s.RW;
-    #pragma unroll 4
-    for (int r = 0; r <= RW; ++r) {
+    const int lane = threadIdx.x & 31;
+    #pragma unroll 2
+    for (int r = threadIdx.x >> 5; r <= RW; r += NT / 32) {
         uint32_t fg = 0, bg = 0;
         {
             const int y = s.sy + r - RW;                       // upper half, half width r
@@ -115,8 +125,9 @@ __device__ __forceinline__ void stage_window(const Src& s, uint32_t* OF, uint32_
                 if (lane == 16) gather(s, y, s.iw0 + 16, xlo, xhi, fg, bg);
             }
         }
-        OF[r * kRowWords + lane] = fg;
-        if (GEN) OB[r * kRowWords + lane] = bg;
+        const int pw = (r << 5) | ((lane + r) & 31);
+        OF[pw] = fg;
+        if (GEN) OB[pw] = bg;
     }
 }
 
@@ -126,6 +137,17 @@ struct Chain {
     int dst_off[kMaxChain];
     int cum[kMaxChain + 1];         // flattened target index space
     int nm;
+};
+
+// per-CTA search state in static shared memory
+struct Ctl {
+    Chain ch;
+    int cnt[3];        // frontier sizes, rotating: wave s reads cnt[s%3], appends to cnt[(s+1)%3]
+    int unsettled;     // in-range targets not yet reached
+    int ncand;
+    int seedcnt;       // general: seeds appended for the next level
+    int settled[3];    // targets reached per wave, rotating like cnt[]
+    int item;
 };
 
 // a target cell was reached at level k with j mask pixels on the path: hop = k + j
@@ -149,11 +171,44 @@ __device__ __forceinline__ int probe_settle(const K2Params& p, const uint32_t* h
     return n;
 }
 
-// One work item = one source of a chain leader.  Returns true when the item must be redone by
-// the general kernel (fast kernel only).
+// Claim the open neighbours of frontier cell e.  fg[d] / bg[d]: this lane claimed the mask /
+// off-mask neighbour in direction d (up, left, right, down); idx[d] its logical index.
 template <bool GEN>
-__device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Chain& ch) {
-    const int lane = threadIdx.x & 31;
+__device__ __forceinline__ void claim_neighbours(bool act, uint32_t e, int o, int RW, uint32_t* OF, uint32_t* OB,
+                                                 bool fg[4], bool bg[4], int idx[4], uint32_t ne[4]) {
+    const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
+    uint32_t vf[4], vb[4], bit[4];
+    int pw[4];
+    bool in[4];
+    #pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        const int ndy = dy + (d == 0 ? -1 : d == 3 ? 1 : 0);
+        const int ncx = cx + (d == 1 ? -1 : d == 2 ? 1 : 0);
+        in[d] = act && abs(ndy) + abs(ncx - o) <= RW;
+        idx[d] = in[d] ? fold_index(ndy, ncx, RW) : 0;
+        pw[d] = phys_word(idx[d]);
+        bit[d] = 1u << (idx[d] & 31);
+        ne[d] = pack_cell(ndy, ncx);
+        vf[d] = OF[pw[d]];
+        vb[d] = GEN ? OB[pw[d]] : 0u;
+    }
+    #pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        fg[d] = false; bg[d] = false;
+        if (in[d]) {
+            if (vf[d] & bit[d]) fg[d] = (atomicAnd(&OF[pw[d]], ~bit[d]) & bit[d]) != 0;
+            else if (GEN && (vb[d] & bit[d])) bg[d] = (atomicAnd(&OB[pw[d]], ~bit[d]) & bit[d]) != 0;
+        }
+    }
+}
+
+// One work item = one source of a chain leader, processed by the whole CTA.  Returns true when
+// the item must be redone by the general kernel (fast kernel only).  All control flow is
+// CTA-uniform (decisions are read from shared memory after a barrier).
+template <bool GEN, int NT>
+__device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
     const uint32_t lt = lanemask_lt();
     const int RW = p.max_px;
     const int nwords = (RW + 1) * kRowWords;
@@ -164,9 +219,11 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
     uint32_t* const OB = OF + (GEN ? nwords : 0);
     uint32_t* const q0 = OB + nwords;
     uint32_t* const hash = q0 + 2 * QCAP;
+    int* const cal0 = (int*)(hash + kHashSize);          // general only: [2][kSeedCal]
     uint32_t* const cand = gscr;
     uint32_t* const gq0 = gscr + kCandCap;
-    uint32_t* const gs0 = gq0 + 2 * (size_t)GQCAP;       // general only
+    uint32_t* const gs0 = gq0 + 2 * (size_t)GQCAP;       // general only: [2][GQCAP]
+    Chain& ch = ctl.ch;
 
     // ---- which chain / source -------------------------------------------------------------
     int lo = 0, hi = p.n_pairs - 1;
@@ -176,8 +233,8 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
     }
     const int si = item - p.work_prefix[lo];
     const axb_pair_desc lead = p.pairs[lo];
-    __syncwarp();
-    if (lane == 0) {
+    __syncthreads();                   // the previous item is finished everywhere
+    if (tid == 0) {
         int q = lo, nm = 0;
         ch.cum[0] = 0;
         while (q >= 0 && nm < kMaxChain) {
@@ -191,7 +248,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
         }
         ch.nm = nm;
     }
-    __syncwarp();
+    __syncthreads();
     const int nm = ch.nm;
     const int total_t = ch.cum[nm];
     if (total_t <= 0) return false;
@@ -201,7 +258,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
     s.sx = p.dets_yx[2 * ((size_t)lead.src_off + si) + 1];
     s.H = p.H; s.W = p.W; s.Wp = p.Wp; s.RW = RW;
     s.mbits = p.mask_bits + (size_t)lead.mask_idx * p.H * p.Wp;
-    s.iw0 = s.sx >> 5;                 // arithmetic shift; only used when the source is in the grid
+    s.iw0 = s.sx >> 5;                 // only used when the source is in the grid
     s.o = s.sx & 31;
     const bool src_in = s.sy >= 0 && s.sy < p.H && s.sx >= 0 && s.sx < p.W;
     const long long r2 = (long long)RW * RW;
@@ -209,12 +266,14 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
 
     int tt = 0;                        // next target of the flattened chain target list
     for (;;) {                         // passes of <= kHashMaxLoad candidates (one on real data)
-        for (int i = lane; i < kHashSize; i += 32) hash[i] = kEmpty;
-        __syncwarp();
-        int ncand = 0;
-        while (tt < total_t) {
-            const int t = tt + lane;
-            bool is_cand = false, self = false, have = t < total_t;
+        for (int i = tid; i < kHashSize; i += NT) hash[i] = kEmpty;
+        if (tid == 0) ctl.ncand = 0;
+        for (;;) {                     // groups of NT targets
+            __syncthreads();
+            if (tt >= total_t || ctl.ncand > kHashMaxLoad - NT) break;
+            const int t = tt + tid;
+            bool is_cand = false, self = false;
+            const bool have = t < total_t;
             int m = 0, j = 0, dy = 0, dx = 0;
             if (have) {
                 while (m + 1 < nm && t >= ch.cum[m + 1]) ++m;
@@ -231,170 +290,196 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                     else if (dy == 0 && dx == 0) self = true;         // start == goal: L = 1 (astar.cpp:67,99)
                     else is_cand = abs(dy) + abs(dx) < RW;            // farther cells need > max_px pixels
                 }
-            }
-            const uint32_t bal = __ballot_sync(kFull, is_cand);
-            const int nb = __popc(bal);
-            if (ncand + nb > kHashMaxLoad) break;                     // next pass starts with this group
-            if (have) {
                 const long long oo = ch.orow[m] + j;
                 p.path_len[oo] = self ? 1 : RW;                       // None -> max_px (AxonDetections.py:736)
                 p.unreachable[oo] = self ? 0 : 1;
                 if (p.wcost) p.wcost[oo] = self ? 0.f : __int_as_float(0x7f800000);
             }
-            if (is_cand) {
-                const uint32_t slot = (uint32_t)ncand + __popc(bal & lt);
-                cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
-                const uint32_t entry = ((uint32_t)fold_index(dy, dx + o, RW) << 13) | slot;
-                uint32_t h = hash_slot(entry >> 13);
-                while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (kHashSize - 1);
+            const uint32_t bal = __ballot_sync(kFull, is_cand);
+            if (bal) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&ctl.ncand, __popc(bal));
+                base = __shfl_sync(kFull, base, 0);
+                if (is_cand) {
+                    const uint32_t slot = (uint32_t)base + __popc(bal & lt);
+                    cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
+                    const uint32_t entry = ((uint32_t)fold_index(dy, dx + o, RW) << 13) | slot;
+                    uint32_t h = hash_slot(entry >> 13);
+                    while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (kHashSize - 1);
+                }
             }
-            ncand += nb;
-            tt += 32;
+            tt += NT;
         }
-        __syncwarp();
-
+        const int ncand = ctl.ncand;
         if (ncand > 0) {
-            stage_window<GEN>(s, OF, OB, lane);
-            __syncwarp();
-            if (lane == 0) {       // close the source cell, seed the search with it
+            stage_window<GEN, NT>(s, OF, OB);
+            __syncthreads();
+            if (tid == 0) {            // close the source cell, seed the search with it
                 const int c = fold_index(0, o, RW);
-                OF[c >> 5] &= ~(1u << (c & 31));
-                if (GEN) OB[c >> 5] &= ~(1u << (c & 31));
+                OF[phys_word(c)] &= ~(1u << (c & 31));
+                if (GEN) OB[phys_word(c)] &= ~(1u << (c & 31));
                 q0[0] = pack_cell(0, o);
-                if (GEN) gs0[0] = pack_cell(0, o);      // tag j = 0
+                if (GEN) gs0[0] = pack_cell(0, o);
+                ctl.cnt[0] = GEN ? 0 : 1; ctl.cnt[1] = 0; ctl.cnt[2] = 0;
+                ctl.settled[0] = 0; ctl.settled[1] = 0; ctl.settled[2] = 0;
+                ctl.unsettled = ncand;
+                ctl.seedcnt = 0;
             }
-            __syncwarp();
+            if (GEN) for (int jj = tid; jj < kSeedCal; jj += NT) cal0[jj] = 1;    // the source: one seed tagged j = 0
+            __threadfence_block();
+            __syncthreads();
 
-            int unsettled = ncand;
-            uint32_t* qcur = q0;       uint32_t* qnxt = q0 + QCAP;
-            uint32_t* gcur = gq0;      uint32_t* gnxt = gq0 + GQCAP;
-
+            int unsettled = ncand;     // CTA-uniform: updated from ctl.settled[] after each barrier
             if (!GEN) {
                 // ---- level 0 only ---------------------------------------------------------
-                int cur_n = 1, j = 0;
+                int cur_n = 1, j = 0, step = 0;
                 bool hit = false, overflow = false;
                 while (cur_n > 0 && unsettled > 0) {
-                    if (j >= RW) { hit = true; break; }       // cells at hop == max_px exist
-                    int nxt_n = 0, my_set = 0;
-                    for (int base = 0; base < cur_n; base += 32) {
+                    if (j >= RW) { hit = true; break; }               // cells at hop == max_px exist
+                    if (cur_n > QCAP + GQCAP) { overflow = true; break; }
+                    const uint32_t* const qcur = q0 + (step & 1) * QCAP;
+                    uint32_t* const qnxt = q0 + ((step + 1) & 1) * QCAP;
+                    const uint32_t* const gcur = gq0 + (size_t)(step & 1) * GQCAP;
+                    uint32_t* const gnxt = gq0 + (size_t)((step + 1) & 1) * GQCAP;
+                    int* const cnt_nxt = &ctl.cnt[(step + 1) % 3];
+                    int* const set_nxt = &ctl.settled[(step + 1) % 3];
+                    for (int base = (tid & ~31); base < cur_n; base += NT) {
                         const int i = base + lane;
                         const bool act = i < cur_n;
                         uint32_t e = 0;
                         if (act) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
-                        const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
+                        bool fg[4], bg[4]; int idx[4]; uint32_t ne[4];
+                        claim_neighbours<false>(act, e, o, RW, OF, OB, fg, bg, idx, ne);
+                        uint32_t bal[4];
+                        int tot = 0;
                         #pragma unroll
-                        for (int d = 0; d < 4; ++d) {
-                            const int ndy = dy + (d == 0 ? -1 : d == 3 ? 1 : 0);
-                            const int ncx = cx + (d == 1 ? -1 : d == 2 ? 1 : 0);
-                            bool claimed = false;
-                            int idx = 0;
-                            if (act && abs(ndy) + abs(ncx - o) <= RW) {
-                                idx = fold_index(ndy, ncx, RW);
-                                const uint32_t bit = 1u << (idx & 31);
-                                if (OF[idx >> 5] & bit) claimed = (atomicAnd(&OF[idx >> 5], ~bit) & bit) != 0;
-                            }
-                            const uint32_t bal = __ballot_sync(kFull, claimed);
-                            if (bal) {
-                                if (claimed) {
-                                    const int slot = nxt_n + __popc(bal & lt);
-                                    const uint32_t ne = pack_cell(ndy, ncx);
-                                    if (slot < QCAP) qnxt[slot] = ne;
-                                    else if (slot - QCAP < GQCAP) gnxt[slot - QCAP] = ne;
-                                    if (j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx, 0, j + 1);
+                        for (int d = 0; d < 4; ++d) { bal[d] = __ballot_sync(kFull, fg[d]); tot += __popc(bal[d]); }
+                        if (tot) {
+                            int pos = 0;
+                            if (lane == 0) pos = atomicAdd(cnt_nxt, tot);
+                            pos = __shfl_sync(kFull, pos, 0);
+                            int my_set = 0;
+                            #pragma unroll
+                            for (int d = 0; d < 4; ++d) {
+                                if (fg[d]) {
+                                    const int slot = pos + __popc(bal[d] & lt);
+                                    if (slot < QCAP) qnxt[slot] = ne[d];
+                                    else if (slot - QCAP < GQCAP) gnxt[slot - QCAP] = ne[d];
+                                    if (j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx[d], 0, j + 1);
                                 }
-                                nxt_n += __popc(bal);
+                                pos += __popc(bal[d]);
                             }
+                            if (my_set) atomicAdd(set_nxt, my_set);
                         }
                     }
-                    if (nxt_n > QCAP + GQCAP) { overflow = true; break; }
-                    unsettled -= __reduce_add_sync(kFull, my_set);
-                    __syncwarp();
-                    uint32_t* tq = qcur; qcur = qnxt; qnxt = tq;
-                    uint32_t* tg = gcur; gcur = gnxt; gnxt = tg;
-                    cur_n = nxt_n;
+                    __syncthreads();
+                    cur_n = *cnt_nxt;
+                    unsettled -= *set_nxt;
+                    if (tid == 0) { ctl.cnt[step % 3] = 0; ctl.settled[step % 3] = 0; }
+                    ++step;
                     ++j;
                 }
                 if (overflow || (!hit && unsettled > 0)) return true;     // level 0 cannot answer: defer
             } else {
                 // ---- all levels -------------------------------------------------------------
-                uint32_t* gs_cur = gs0;   uint32_t* gs_nxt = gs0 + GQCAP;
                 int n_seeds = 1;
                 for (int k = 0; k <= RW && n_seeds > 0 && unsettled > 0; ++k) {
-                    int sp = 0, n_next = 0, cur_n = 0;
-                    int j = (int)(gs_cur[0] >> 21);
+                    const uint32_t* const gs_cur = gs0 + (size_t)(k & 1) * GQCAP;
+                    uint32_t* const gs_nxt = gs0 + (size_t)((k + 1) & 1) * GQCAP;
+                    const int* const cal_cur = cal0 + (k & 1) * kSeedCal;      // #seeds tagged <= j
+                    int* const cal_nxt = cal0 + ((k + 1) & 1) * kSeedCal;
+                    int j = 0;
+                    while (cal_cur[j] == 0) ++j;                      // first seeded j of this level
+                    const int jstart = j;
+                    int sp = 0, nlist = 0, step = 0;
                     bool hit = false;
                     for (;;) {
-                        int ns = 0;                  // seeds tagged j (the list is sorted by tag)
-                        for (int pos = sp; pos < n_seeds; pos += 32) {
-                            const int i = pos + lane;
-                            const bool match = i < n_seeds && (int)(gs_cur[i] >> 21) == j;
-                            const int c = __popc(__ballot_sync(kFull, match));
-                            ns += c;
-                            if (c < 32) break;
-                        }
-                        if (cur_n + ns == 0) {
-                            if (sp >= n_seeds) break;              // level exhausted
-                            j = (int)(gs_cur[sp] >> 21);
+                        const int send = cal_cur[j];
+                        const int tot_n = nlist + (send - sp);
+                        if (tot_n == 0) {
+                            if (sp >= n_seeds) break;                 // level exhausted
+                            if (tid == 0) cal_nxt[j] = ctl.seedcnt;
+                            ++j;
                             continue;
                         }
-                        if (k + j >= RW) { hit = true; break; }     // cells at hop == max_px exist
+                        if (k + j >= RW) { hit = true; break; }       // cells at hop == max_px exist
                         if (unsettled <= 0) break;
-                        const int tot = cur_n + ns;
-                        int nxt_n = 0, my_set = 0;
-                        for (int base = 0; base < tot; base += 32) {
+                        const uint32_t* const qcur = q0 + (step & 1) * QCAP;
+                        uint32_t* const qnxt = q0 + ((step + 1) & 1) * QCAP;
+                        const uint32_t* const gcur = gq0 + (size_t)(step & 1) * GQCAP;
+                        uint32_t* const gnxt = gq0 + (size_t)((step + 1) & 1) * GQCAP;
+                        int* const cnt_nxt = &ctl.cnt[(step + 1) % 3];
+                        int* const set_nxt = &ctl.settled[(step + 1) % 3];
+                        for (int base = (tid & ~31); base < tot_n; base += NT) {
                             const int i = base + lane;
-                            const bool act = i < tot;
+                            const bool act = i < tot_n;
                             uint32_t e = 0;
                             bool seed = false;
                             if (act) {
-                                if (i < cur_n) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
-                                else { e = gs_cur[sp + (i - cur_n)] & 0x1FFFFFu; seed = true; }
+                                if (i < nlist) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
+                                else { e = gs_cur[sp + (i - nlist)]; seed = true; }
                             }
-                            const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
-                            // off-mask cells settle when their level starts consuming them: by then
-                            // no lower level has reached hop max_px
-                            if (seed && k > 0) my_set += probe_settle(p, hash, cand, ch, (uint32_t)fold_index(dy, cx, RW), k, j);
+                            int my_set = 0;
+                            // off-mask cells settle when their level starts consuming them: by then no
+                            // lower level has reached hop max_px
+                            if (seed && k > 0)
+                                my_set += probe_settle(p, hash, cand, ch, (uint32_t)fold_index((int)(e >> 11) - 512, (int)(e & 2047u) - 512, RW), k, j);
+                            bool fg[4], bg[4]; int idx[4]; uint32_t ne[4];
+                            claim_neighbours<true>(act, e, o, RW, OF, OB, fg, bg, idx, ne);
+                            uint32_t bf[4], bb[4];
+                            int totf = 0, totb = 0;
                             #pragma unroll
                             for (int d = 0; d < 4; ++d) {
-                                const int ndy = dy + (d == 0 ? -1 : d == 3 ? 1 : 0);
-                                const int ncx = cx + (d == 1 ? -1 : d == 2 ? 1 : 0);
-                                bool got_fg = false, got_bg = false;
-                                int idx = 0;
-                                if (act && abs(ndy) + abs(ncx - o) <= RW) {
-                                    idx = fold_index(ndy, ncx, RW);
-                                    const uint32_t bit = 1u << (idx & 31);
-                                    if (OF[idx >> 5] & bit) got_fg = (atomicAnd(&OF[idx >> 5], ~bit) & bit) != 0;
-                                    else if (OB[idx >> 5] & bit) got_bg = (atomicAnd(&OB[idx >> 5], ~bit) & bit) != 0;
-                                }
-                                const uint32_t bf = __ballot_sync(kFull, got_fg);
-                                const uint32_t bb = __ballot_sync(kFull, got_bg);
-                                if (bf) {
-                                    if (got_fg) {
-                                        const int slot = nxt_n + __popc(bf & lt);
-                                        const uint32_t ne = pack_cell(ndy, ncx);
-                                        if (slot < QCAP) qnxt[slot] = ne; else gnxt[slot - QCAP] = ne;
-                                        if (k + j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx, k, j + 1);
+                                bf[d] = __ballot_sync(kFull, fg[d]); totf += __popc(bf[d]);
+                                bb[d] = __ballot_sync(kFull, bg[d]); totb += __popc(bb[d]);
+                            }
+                            if (totf) {
+                                int pos = 0;
+                                if (lane == 0) pos = atomicAdd(cnt_nxt, totf);
+                                pos = __shfl_sync(kFull, pos, 0);
+                                #pragma unroll
+                                for (int d = 0; d < 4; ++d) {
+                                    if (fg[d]) {
+                                        const int slot = pos + __popc(bf[d] & lt);
+                                        if (slot < QCAP) qnxt[slot] = ne[d]; else gnxt[slot - QCAP] = ne[d];
+                                        if (k + j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx[d], k, j + 1);
                                     }
-                                    nxt_n += __popc(bf);
-                                }
-                                if (bb) {
-                                    if (got_bg) gs_nxt[n_next + __popc(bb & lt)] = ((uint32_t)j << 21) | pack_cell(ndy, ncx);
-                                    n_next += __popc(bb);
+                                    pos += __popc(bf[d]);
                                 }
                             }
+                            if (totb) {
+                                int pos = 0;
+                                if (lane == 0) pos = atomicAdd(&ctl.seedcnt, totb);
+                                pos = __shfl_sync(kFull, pos, 0);
+                                #pragma unroll
+                                for (int d = 0; d < 4; ++d) {
+                                    if (bg[d]) gs_nxt[pos + __popc(bb[d] & lt)] = ne[d];
+                                    pos += __popc(bb[d]);
+                                }
+                            }
+                            if (my_set) atomicAdd(set_nxt, my_set);
                         }
-                        unsettled -= __reduce_add_sync(kFull, my_set);
-                        __syncwarp();
-                        uint32_t* tq = qcur; qcur = qnxt; qnxt = tq;
-                        uint32_t* tg = gcur; gcur = gnxt; gnxt = tg;
-                        sp += ns;
-                        cur_n = nxt_n;
+                        __syncthreads();
+                        nlist = *cnt_nxt;
+                        unsettled -= *set_nxt;
+                        if (tid == 0) { ctl.cnt[step % 3] = 0; ctl.settled[step % 3] = 0; cal_nxt[j] = ctl.seedcnt; }
+                        __syncthreads();       // seedcnt is read before the next wave appends to it
+                        sp = send;
+                        ++step;
                         ++j;
                     }
+                    // ---- level end: complete the next level's calendar ------------------------------
+                    __syncthreads();
+                    const int total_next = ctl.seedcnt;
+                    for (int jj = tid; jj < kSeedCal; jj += NT) {
+                        if (jj >= j) cal_nxt[jj] = total_next;
+                        else if (jj < jstart) cal_nxt[jj] = 0;
+                    }
+                    __syncthreads();
+                    if (tid == 0) { ctl.seedcnt = 0; ctl.cnt[0] = 0; ctl.cnt[1] = 0; ctl.cnt[2] = 0; ctl.settled[0] = 0; ctl.settled[1] = 0; ctl.settled[2] = 0; }
+                    __syncthreads();
                     if (hit) break;                    // k* = k: every deeper target stays None
-                    uint32_t* ts = gs_cur; gs_cur = gs_nxt; gs_nxt = ts;
-                    n_seeds = n_next;
-                    __syncwarp();
+                    n_seeds = total_next;
                 }
             }
         }
@@ -405,37 +490,36 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
 
 }  // namespace
 
-__global__ void __launch_bounds__(32, kFastCtasPerSm) k2_fast_kernel(const K2Params p) {
+__global__ void __launch_bounds__(kK2Threads, kFastCtasPerSm) k2_fast_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
-    __shared__ Chain ch;
+    __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
     const int total = p.work_prefix[p.n_pairs];
     for (;;) {
-        int item = 0;
-        if (threadIdx.x == 0) item = atomicAdd(&p.counters[0], 1);
-        item = __shfl_sync(kFull, item, 0);
+        __syncthreads();
+        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[0], 1);
+        __syncthreads();
+        const int item = ctl.item;
         if (item >= total) break;
-        const bool defer = run_item<false>(p, item, smem, gscr, ch);
+        const bool defer = run_item<false, kK2Threads>(p, item, smem, gscr, ctl);
         if (defer && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
-        __syncwarp();
     }
 }
 
-__global__ void __launch_bounds__(32, 1) k2_general_kernel(const K2Params p) {
+__global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
-    __shared__ Chain ch;
+    __shared__ Ctl ctl;
     uint32_t* const gscr = p.gen_scratch + (size_t)blockIdx.x * kGenScratchWords;
     const int total = p.counters[1];
     for (;;) {
-        int t = 0;
-        if (threadIdx.x == 0) t = atomicAdd(&p.counters[2], 1);
-        t = __shfl_sync(kFull, t, 0);
+        __syncthreads();
+        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[2], 1);
+        __syncthreads();
+        const int t = ctl.item;
         if (t >= total) break;
-        run_item<true>(p, p.gen_list[t], smem, gscr, ch);
-        __syncwarp();
+        run_item<true, kK2Threads>(p, p.gen_list[t], smem, gscr, ctl);
     }
 }
-
 // Chains + prefix sums + counter reset, one CTA.
 //   same key = same (mask_idx, src_off, n_src): the searches of the two pairs are identical, only
 //   the targets differ.  prev/next link same-key pairs inside a +-kChainWindow index window; a
@@ -519,7 +603,7 @@ void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {
         cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         attr_set = true;
     }
-    k2_fast_kernel<<<grid, 32, k2_fast_smem_bytes(p.max_px), stream>>>(p);
+    k2_fast_kernel<<<grid, kK2Threads, k2_fast_smem_bytes(p.max_px), stream>>>(p);
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {
@@ -528,7 +612,7 @@ void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {
         cudaFuncSetAttribute(k2_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_gen_smem_bytes(AXB_MAX_PX));
         attr_set = true;
     }
-    k2_general_kernel<<<grid, 32, k2_gen_smem_bytes(p.max_px), stream>>>(p);
+    k2_general_kernel<<<grid, kK2Threads, k2_gen_smem_bytes(p.max_px), stream>>>(p);
 }
 
 }  // namespace axb
