@@ -22,7 +22,7 @@ constexpr int kMaxChain = 4;          // frame pairs that share one source searc
 constexpr int kHashSize = 1024;       // target-cell hash (u32 entries) in shared memory
 constexpr int kHashMaxLoad = 640;     // candidates per search pass
 constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
-constexpr int kK2Threads = 128;       // one CTA (4 warps) per source search
+constexpr int kK2Threads = 256;       // one CTA (8 warps) per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
 // fast kernel (level 0 only): 3 CTAs per SM
 constexpr int kFastQCap = 768;        // frontier entries per buffer in shared memory

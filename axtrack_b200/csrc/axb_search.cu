@@ -20,7 +20,7 @@
 // path_length = k + j + 1 if that is <= max_px.
 //
 // Mapping to the SM.  A search is ~max_px dependent wavefronts of a few hundred cells: latency
-// bound.  One CTA of kK2Threads (4 warps) per source, one __syncthreads per wavefront, and
+// bound.  One CTA of kK2Threads (8 warps) per source, one __syncthreads per wavefront, and
 // throughput from 3 resident CTAs per SM x 148 SMs of independent searches.
 //   k2_fast_kernel     level 0 only (the answer for every source whose mask component reaches
 //                      hop max_px or contains all its in-range targets -- nearly all of them on
@@ -28,8 +28,9 @@
 //                      in the folded-diamond layout of axb_common.cuh (rows rotated by their index
 //                      so that a vertical run of cells spreads over the 32 banks), staged with
 //                      aligned 128 B row reads of the bit-packed mask; claiming a cell is one
-//                      shared-memory atomicAnd; the frontier queue (shared, global overflow) is
-//                      appended with one warp-aggregated atomicAdd per 32 cells; targets are
+//                      shared-memory atomicAnd by one lane per (frontier cell, direction); the
+//                      frontier queue (shared, global overflow) is appended with one
+//                      warp-aggregated atomicAdd per 32 lanes; targets are
 //                      found through a 4 KB shared hash of their window cells probed by the lane
 //                      that claims a cell.  75 KB per CTA -> 3 CTAs per SM, persistent over a
 //                      ticket counter.
@@ -171,37 +172,6 @@ __device__ __forceinline__ int probe_settle(const K2Params& p, const uint32_t* h
     return n;
 }
 
-// Claim the open neighbours of frontier cell e.  fg[d] / bg[d]: this lane claimed the mask /
-// off-mask neighbour in direction d (up, left, right, down); idx[d] its logical index.
-template <bool GEN>
-__device__ __forceinline__ void claim_neighbours(bool act, uint32_t e, int o, int RW, uint32_t* OF, uint32_t* OB,
-                                                 bool fg[4], bool bg[4], int idx[4], uint32_t ne[4]) {
-    const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
-    uint32_t vf[4], vb[4], bit[4];
-    int pw[4];
-    bool in[4];
-    #pragma unroll
-    for (int d = 0; d < 4; ++d) {
-        const int ndy = dy + (d == 0 ? -1 : d == 3 ? 1 : 0);
-        const int ncx = cx + (d == 1 ? -1 : d == 2 ? 1 : 0);
-        in[d] = act && abs(ndy) + abs(ncx - o) <= RW;
-        idx[d] = in[d] ? fold_index(ndy, ncx, RW) : 0;
-        pw[d] = phys_word(idx[d]);
-        bit[d] = 1u << (idx[d] & 31);
-        ne[d] = pack_cell(ndy, ncx);
-        vf[d] = OF[pw[d]];
-        vb[d] = GEN ? OB[pw[d]] : 0u;
-    }
-    #pragma unroll
-    for (int d = 0; d < 4; ++d) {
-        fg[d] = false; bg[d] = false;
-        if (in[d]) {
-            if (vf[d] & bit[d]) fg[d] = (atomicAnd(&OF[pw[d]], ~bit[d]) & bit[d]) != 0;
-            else if (GEN && (vb[d] & bit[d])) bg[d] = (atomicAnd(&OB[pw[d]], ~bit[d]) & bit[d]) != 0;
-        }
-    }
-}
-
 // One work item = one source of a chain leader, processed by the whole CTA.  Returns true when
 // the item must be redone by the general kernel (fast kernel only).  All control flow is
 // CTA-uniform (decisions are read from shared memory after a barrier).
@@ -330,6 +300,12 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
             __syncthreads();
 
             int unsettled = ncand;     // CTA-uniform: updated from ctl.settled[] after each barrier
+            // One lane per (frontier cell, direction): the direction of a thread never changes.
+            const int dir = tid & 3;
+            const int ddy = dir == 0 ? -1 : dir == 3 ? 1 : 0;
+            const int dcx = dir == 1 ? -1 : dir == 2 ? 1 : 0;
+            // Expanded cells sit at hop <= max_px-1, so every neighbour lies inside the diamond: no
+            // bound check; pixels outside the image were staged as closed.
             if (!GEN) {
                 // ---- level 0 only ---------------------------------------------------------
                 int cur_n = 1, j = 0, step = 0;
@@ -343,33 +319,35 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                     uint32_t* const gnxt = gq0 + (size_t)((step + 1) & 1) * GQCAP;
                     int* const cnt_nxt = &ctl.cnt[(step + 1) % 3];
                     int* const set_nxt = &ctl.settled[(step + 1) % 3];
-                    for (int base = (tid & ~31); base < cur_n; base += NT) {
-                        const int i = base + lane;
-                        const bool act = i < cur_n;
-                        uint32_t e = 0;
-                        if (act) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
-                        bool fg[4], bg[4]; int idx[4]; uint32_t ne[4];
-                        claim_neighbours<false>(act, e, o, RW, OF, OB, fg, bg, idx, ne);
-                        uint32_t bal[4];
-                        int tot = 0;
-                        #pragma unroll
-                        for (int d = 0; d < 4; ++d) { bal[d] = __ballot_sync(kFull, fg[d]); tot += __popc(bal[d]); }
-                        if (tot) {
+                    const int ntask = cur_n * 4;
+                    for (int base = (tid & ~31); base < ntask; base += NT) {
+                        const int i = (base + lane) >> 2;
+                        bool got = false;
+                        int idx = 0;
+                        uint32_t ne = 0;
+                        if (i < cur_n) {
+                            const uint32_t e = i < QCAP ? qcur[i] : gcur[i - QCAP];
+                            const int ndy = (int)(e >> 11) - 512 + ddy, ncx = (int)(e & 2047u) - 512 + dcx;
+                            idx = fold_index(ndy, ncx, RW);
+                            ne = pack_cell(ndy, ncx);
+                            const int pw = phys_word(idx);
+                            const uint32_t bit = 1u << (idx & 31);
+                            if (OF[pw] & bit) got = (atomicAnd(&OF[pw], ~bit) & bit) != 0;
+                        }
+                        const uint32_t bal = __ballot_sync(kFull, got);
+                        if (bal) {
                             int pos = 0;
-                            if (lane == 0) pos = atomicAdd(cnt_nxt, tot);
+                            if (lane == 0) pos = atomicAdd(cnt_nxt, __popc(bal));
                             pos = __shfl_sync(kFull, pos, 0);
-                            int my_set = 0;
-                            #pragma unroll
-                            for (int d = 0; d < 4; ++d) {
-                                if (fg[d]) {
-                                    const int slot = pos + __popc(bal[d] & lt);
-                                    if (slot < QCAP) qnxt[slot] = ne[d];
-                                    else if (slot - QCAP < GQCAP) gnxt[slot - QCAP] = ne[d];
-                                    if (j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx[d], 0, j + 1);
+                            if (got) {
+                                const int slot = pos + __popc(bal & lt);
+                                if (slot < QCAP) qnxt[slot] = ne;
+                                else if (slot - QCAP < GQCAP) gnxt[slot - QCAP] = ne;
+                                if (j + 1 < RW) {
+                                    const int ns = probe_settle(p, hash, cand, ch, (uint32_t)idx, 0, j + 1);
+                                    if (ns) atomicAdd(set_nxt, ns);
                                 }
-                                pos += __popc(bal[d]);
                             }
-                            if (my_set) atomicAdd(set_nxt, my_set);
                         }
                     }
                     __syncthreads();
@@ -410,52 +388,46 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                         uint32_t* const gnxt = gq0 + (size_t)((step + 1) & 1) * GQCAP;
                         int* const cnt_nxt = &ctl.cnt[(step + 1) % 3];
                         int* const set_nxt = &ctl.settled[(step + 1) % 3];
-                        for (int base = (tid & ~31); base < tot_n; base += NT) {
-                            const int i = base + lane;
-                            const bool act = i < tot_n;
-                            uint32_t e = 0;
-                            bool seed = false;
-                            if (act) {
+                        const int ntask = tot_n * 4;
+                        for (int base = (tid & ~31); base < ntask; base += NT) {
+                            const int i = (base + lane) >> 2;
+                            bool got_fg = false, got_bg = false;
+                            int idx = 0, my_set = 0;
+                            uint32_t ne = 0;
+                            if (i < tot_n) {
+                                uint32_t e;
+                                bool seed = false;
                                 if (i < nlist) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
                                 else { e = gs_cur[sp + (i - nlist)]; seed = true; }
+                                const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
+                                // off-mask cells settle when their level starts consuming them: by then no
+                                // lower level has reached hop max_px
+                                if (seed && k > 0 && dir == 0)
+                                    my_set += probe_settle(p, hash, cand, ch, (uint32_t)fold_index(dy, cx, RW), k, j);
+                                idx = fold_index(dy + ddy, cx + dcx, RW);
+                                ne = pack_cell(dy + ddy, cx + dcx);
+                                const int pw = phys_word(idx);
+                                const uint32_t bit = 1u << (idx & 31);
+                                if (OF[pw] & bit) got_fg = (atomicAnd(&OF[pw], ~bit) & bit) != 0;
+                                else if (OB[pw] & bit) got_bg = (atomicAnd(&OB[pw], ~bit) & bit) != 0;
                             }
-                            int my_set = 0;
-                            // off-mask cells settle when their level starts consuming them: by then no
-                            // lower level has reached hop max_px
-                            if (seed && k > 0)
-                                my_set += probe_settle(p, hash, cand, ch, (uint32_t)fold_index((int)(e >> 11) - 512, (int)(e & 2047u) - 512, RW), k, j);
-                            bool fg[4], bg[4]; int idx[4]; uint32_t ne[4];
-                            claim_neighbours<true>(act, e, o, RW, OF, OB, fg, bg, idx, ne);
-                            uint32_t bf[4], bb[4];
-                            int totf = 0, totb = 0;
-                            #pragma unroll
-                            for (int d = 0; d < 4; ++d) {
-                                bf[d] = __ballot_sync(kFull, fg[d]); totf += __popc(bf[d]);
-                                bb[d] = __ballot_sync(kFull, bg[d]); totb += __popc(bb[d]);
-                            }
-                            if (totf) {
+                            const uint32_t bf = __ballot_sync(kFull, got_fg);
+                            const uint32_t bb = __ballot_sync(kFull, got_bg);
+                            if (bf) {
                                 int pos = 0;
-                                if (lane == 0) pos = atomicAdd(cnt_nxt, totf);
+                                if (lane == 0) pos = atomicAdd(cnt_nxt, __popc(bf));
                                 pos = __shfl_sync(kFull, pos, 0);
-                                #pragma unroll
-                                for (int d = 0; d < 4; ++d) {
-                                    if (fg[d]) {
-                                        const int slot = pos + __popc(bf[d] & lt);
-                                        if (slot < QCAP) qnxt[slot] = ne[d]; else gnxt[slot - QCAP] = ne[d];
-                                        if (k + j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx[d], k, j + 1);
-                                    }
-                                    pos += __popc(bf[d]);
+                                if (got_fg) {
+                                    const int slot = pos + __popc(bf & lt);
+                                    if (slot < QCAP) qnxt[slot] = ne; else gnxt[slot - QCAP] = ne;
+                                    if (k + j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx, k, j + 1);
                                 }
                             }
-                            if (totb) {
+                            if (bb) {
                                 int pos = 0;
-                                if (lane == 0) pos = atomicAdd(&ctl.seedcnt, totb);
+                                if (lane == 0) pos = atomicAdd(&ctl.seedcnt, __popc(bb));
                                 pos = __shfl_sync(kFull, pos, 0);
-                                #pragma unroll
-                                for (int d = 0; d < 4; ++d) {
-                                    if (bg[d]) gs_nxt[pos + __popc(bb[d] & lt)] = ne[d];
-                                    pos += __popc(bb[d]);
-                                }
+                                if (got_bg) gs_nxt[pos + __popc(bb & lt)] = ne;
                             }
                             if (my_set) atomicAdd(set_nxt, my_set);
                         }
