@@ -211,7 +211,7 @@ def run_reference(args, wl):
 def run_b200(args, wl):
     import torch
     import torch.distributed as dist
-    from axtrack_b200 import ops, pipeline, host
+    from axtrack_b200 import ops, pipeline, host, sharding
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -231,24 +231,11 @@ def run_b200(args, wl):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     ctx = ops.get_context(dev)
 
-    recv = {}
-
     def gather_to_rank0(res):
         if world == 1:
             return
-        sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
-        dist.all_gather(sizes, torch.tensor([res.path_len.numel()], dtype=torch.int64, device=dev))
-        opsl = []
-        if rank == 0:
-            for r in range(1, world):
-                n = int(sizes[r].item())
-                if r not in recv or recv[r][0].numel() < n:
-                    recv[r] = (torch.empty(n, dtype=torch.int32, device=dev), torch.empty(n, dtype=torch.uint8, device=dev))
-                opsl += [dist.P2POp(dist.irecv, recv[r][0][:n], r), dist.P2POp(dist.irecv, recv[r][1][:n], r)]
-        else:
-            opsl += [dist.P2POp(dist.isend, res.path_len, 0), dist.P2POp(dist.isend, res.unreachable, 0)]
-        for w in dist.batch_isend_irecv(opsl):
-            w.wait()
+        shapes = torch.from_numpy(np.stack([res.pairs['n_src'], res.pairs['n_dst']], 1).astype(np.int64).reshape(-1, 2))
+        sharding.gather_to_rank0(res.path_len, res.unreachable, shapes)
 
     def step():
         res = pipeline.associate_frames(Yd, td, md, max_px=MAX_PX, max_num_misses=MAX_MISSES, want_cost=False, t0=t0)

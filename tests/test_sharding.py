@@ -1,0 +1,72 @@
+"""Host logic of the timepoint sharding (N > 1 path) on CPU: partition, key order, and the
+gather of per-pair matrices to rank 0 over gloo with world_size 2 and 3.  The per-rank "compute"
+here is the oracle (checker) so that the assembled result can be compared with a single-rank
+run; the CUDA path is covered by the -m gpu tests and bench.py --gpus N."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from axtrack_b200 import sharding, synth
+from axtrack_b200.host import frame_pair_keys
+
+
+def test_partition_covers_all_pairs():
+    for T in (1, 2, 3, 7, 100, 2000):
+        for world in (1, 2, 3, 4, 8):
+            for mm in (0, 1, 3):
+                blocks = sharding.partition(T, world, mm)
+                keys = [k for b in blocks for k in sharding.global_keys(b, mm)]
+                assert keys == frame_pair_keys(T, mm), (T, world, mm)
+                for first, own, stop in blocks:
+                    assert first == max(0, own - (mm + 1)) and own <= stop
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, T, out_path):
+    import oracle
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        mask = synth.make_mask(200, 240, 4, pitch=(40, 80), width=(4, 9))
+        tracks = synth.make_tracks(mask, 12, T, 4, off_mask_frac=0.2)
+        tracks[2] = np.zeros((0, 2), np.int32)          # an empty frame
+        blocks = sharding.partition(T, world, 1)
+        pls, uns, shapes = [], [], []
+        for t, tb in sharding.global_keys(blocks[rank], 1):
+            pl, un, _ = oracle.cost_matrix_rule(mask, tracks[tb], tracks[t], 60)
+            pls.append(pl.reshape(-1)); uns.append(un.reshape(-1)); shapes.append((len(tracks[tb]), len(tracks[t])))
+        cat = lambda xs, dt: torch.from_numpy(np.concatenate(xs).astype(dt)) if xs else torch.zeros(0, dtype=torch.from_numpy(np.zeros(0, dt)).dtype)
+        g = sharding.gather_to_rank0(cat(pls, np.int32), cat(uns, np.uint8),
+                                     torch.tensor(shapes, dtype=torch.int64).reshape(-1, 2))
+        if rank == 0:
+            res = sharding.assemble(g, blocks, 1)
+            assert list(res) == frame_pair_keys(T, 1)
+            for (t, tb), (pl, un) in res.items():
+                rpl, run, _ = oracle.cost_matrix_rule(mask, tracks[tb], tracks[t], 60)
+                assert np.array_equal(pl, rpl) and np.array_equal(un, run), (t, tb)
+            open(out_path, 'w').write('ok %d' % len(res))
+        else:
+            assert g is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_gather_gloo(world, tmp_path):
+    out = str(tmp_path / 'ok.txt')
+    T = 7
+    mp.spawn(_worker, args=(world, _free_port(), T, out), nprocs=world, join=True)
+    assert open(out).read() == 'ok %d' % len(frame_pair_keys(T, 1))
