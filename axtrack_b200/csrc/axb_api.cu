@@ -281,7 +281,7 @@ int axb_cost_matrix_host(axb_ctx* c, const uint8_t* mask_host, int H, int W,
 
 int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
                    int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist, int cap,
-                   float* pre_conf_dev, int32_t* pre_yx_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
+                   float* pre_conf_dev, int32_t* pre_yx_dev, int32_t* pre_cell_dev, int32_t* n_pre_dev,
                    float* conf_dev, int32_t* yx_dev, int32_t* keep_idx_dev, int32_t* n_out_dev, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (F < 0 || ntiles <= 0 || Sx <= 0 || Sy <= 0 || tilesize <= 0 || cap <= 0 || nms_dist < 0 || nms_dist > 30000)
@@ -301,7 +301,7 @@ int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
     axb::K1Params p;
     p.Y = Y_dev; p.tile_yx = tile_yx_dev; p.F = F; p.ntiles = ntiles; p.Sx = Sx; p.Sy = Sy; p.tilesize = tilesize;
     p.conf_thr = conf_thr; p.nms_d2 = nms_dist * nms_dist; p.cap = cap;
-    p.pre_conf = pre_conf_dev; p.pre_yx = pre_yx_dev; p.pre_tile = pre_tile_dev; p.n_pre = n_pre_dev;
+    p.pre_conf = pre_conf_dev; p.pre_yx = pre_yx_dev; p.pre_cell = pre_cell_dev; p.n_pre = n_pre_dev;
     p.conf = conf_dev; p.yx = yx_dev; p.keep_idx = keep_idx_dev; p.n_out = n_out_dev;
     p.scratch = c->k1_scratch; p.scratch_per_frame = per_frame; p.npad = npad; p.err_flags = c->status_dev + 1;
     axb::launch_k1(p, (cudaStream_t)stream);
@@ -312,7 +312,7 @@ int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
 
 int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_host,
                         int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist, int cap,
-                        float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_tile_host, int32_t* n_pre_host,
+                        float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_cell_host, int32_t* n_pre_host,
                         float* conf_host, int32_t* yx_host, int32_t* keep_idx_host, int32_t* n_out_host) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (F < 0 || ntiles <= 0 || Sx <= 0 || Sy <= 0 || cap <= 0) return bad_arg(c, "axb_decode_nms_host: bad size");
@@ -335,7 +335,7 @@ int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_
     AXB_CUDA(c, cudaMemcpyAsync(dY, Y_host, nY, cudaMemcpyHostToDevice, s));
     AXB_CUDA(c, cudaMemcpyAsync(dT, tile_yx_host, nT, cudaMemcpyHostToDevice, s));
     rc = axb_decode_nms(c, dY, dT, F, ntiles, Sx, Sy, tilesize, conf_thr, nms_dist, cap,
-                        pre_conf_host ? d_pconf : nullptr, pre_yx_host ? d_pyx : nullptr, pre_tile_host ? d_ptile : nullptr,
+                        pre_conf_host ? d_pconf : nullptr, pre_yx_host ? d_pyx : nullptr, pre_cell_host ? d_ptile : nullptr,
                         d_npre, d_conf, d_yx, d_keep, d_nout, s);
     if (rc != AXB_OK) return rc;
     AXB_CUDA(c, cudaMemcpyAsync(n_pre_host, d_npre, nF, cudaMemcpyDeviceToHost, s));
@@ -345,7 +345,7 @@ int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_
     AXB_CUDA(c, cudaMemcpyAsync(keep_idx_host, d_keep, nFC, cudaMemcpyDeviceToHost, s));
     if (pre_conf_host) AXB_CUDA(c, cudaMemcpyAsync(pre_conf_host, d_pconf, nFC, cudaMemcpyDeviceToHost, s));
     if (pre_yx_host) AXB_CUDA(c, cudaMemcpyAsync(pre_yx_host, d_pyx, 2 * nFC, cudaMemcpyDeviceToHost, s));
-    if (pre_tile_host) AXB_CUDA(c, cudaMemcpyAsync(pre_tile_host, d_ptile, nFC, cudaMemcpyDeviceToHost, s));
+    if (pre_cell_host) AXB_CUDA(c, cudaMemcpyAsync(pre_cell_host, d_ptile, nFC, cudaMemcpyDeviceToHost, s));
     return axb_status(c, s, nullptr);
 }
 

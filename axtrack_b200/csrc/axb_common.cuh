@@ -78,7 +78,7 @@ struct K1Params {
     float conf_thr;
     int nms_d2;                  // nms_dist^2
     int cap;
-    float* pre_conf; int32_t* pre_yx; int32_t* pre_tile; int32_t* n_pre;
+    float* pre_conf; int32_t* pre_yx; int32_t* pre_cell; int32_t* n_pre;
     float* conf; int32_t* yx; int32_t* keep_idx; int32_t* n_out;
     uint8_t* scratch;            // per frame workspace
     size_t scratch_per_frame;

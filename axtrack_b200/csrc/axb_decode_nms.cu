@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(NT) k1_decode_nms_kernel(const K1Params p) {
         w.key[pi] = ((unsigned long long)ordered_bits(conf) << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)pi);
         if (p.pre_conf) p.pre_conf[(size_t)f * p.cap + pi] = conf;
         if (p.pre_yx) { p.pre_yx[((size_t)f * p.cap + pi) * 2] = fy; p.pre_yx[((size_t)f * p.cap + pi) * 2 + 1] = fx; }
-        if (p.pre_tile) p.pre_tile[(size_t)f * p.cap + pi] = tile;
+        if (p.pre_cell) p.pre_cell[(size_t)f * p.cap + pi] = g;
     }
     int nsort = 1;
     while (nsort < n_pre) nsort <<= 1;

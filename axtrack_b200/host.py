@@ -49,11 +49,11 @@ class HostAssociator:
                      yx=np.empty((F, cap, 2), np.int32), keep_idx=np.empty((F, cap), np.int32))
             if want_pre:
                 o.update(pre_conf=np.empty((F, cap), np.float32), pre_yx=np.empty((F, cap, 2), np.int32),
-                         pre_tile=np.empty((F, cap), np.int32))
+                         pre_cell=np.empty((F, cap), np.int32))
         rc = self.lib.axb_decode_nms_host(
             self.ctx.handle, _ptr(Y), _ptr(tile_yx), F, ntiles, Sx, Sy, int(tilesize),
             ctypes.c_float(float(np.float32(conf_thr))), int(nms_dist), cap,
-            _ptr(o.get('pre_conf')), _ptr(o.get('pre_yx')), _ptr(o.get('pre_tile')), _ptr(o['n_pre']),
+            _ptr(o.get('pre_conf')), _ptr(o.get('pre_yx')), _ptr(o.get('pre_cell')), _ptr(o['n_pre']),
             _ptr(o['conf']), _ptr(o['yx']), _ptr(o['keep_idx']), _ptr(o['n_out']))
         self._raise(rc)
         return o

@@ -134,7 +134,7 @@ def decode_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23, cap=None, w
 
     Y float32 CUDA [F, ntiles, Sx, Sy, 3]; tile_yx int32 CUDA [ntiles, 2].
     Returns dict of CUDA tensors: n_pre [F], pre_conf [F,cap], pre_yx [F,cap,2] (y, x),
-    pre_tile [F,cap], n_out [F], conf [F,cap], yx [F,cap,2] (y, x), keep_idx [F,cap].
+    pre_cell [F,cap] (tile*Sx*Sy + ix*Sy + iy), n_out [F], conf [F,cap], yx [F,cap,2] (y, x), keep_idx [F,cap].
     Replaces _yolo_Y2pandas_det + stitch_tiles + _non_max_supression
     (AxonDetections.py:178-278, Timelapse.py:166-197)."""
     Y = _need_cuda(Y, 'Y', torch.float32)
@@ -155,12 +155,12 @@ def decode_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23, cap=None, w
     if want_pre:
         o.update(pre_conf=torch.empty((F, cap), dtype=torch.float32, device=dev),
                  pre_yx=torch.empty((F, cap, 2), dtype=torch.int32, device=dev),
-                 pre_tile=torch.empty((F, cap), dtype=torch.int32, device=dev))
+                 pre_cell=torch.empty((F, cap), dtype=torch.int32, device=dev))
     ptr = lambda k: o[k].data_ptr() if k in o else None
     ctx.check(ctx.lib.axb_decode_nms(
         ctx.handle, Y.data_ptr(), tile_yx.data_ptr(), F, ntiles, Sx, Sy, int(tilesize),
         ctypes.c_float(float(np.float32(conf_thr))), int(nms_dist), int(cap),
-        ptr('pre_conf'), ptr('pre_yx'), ptr('pre_tile'), o['n_pre'].data_ptr(),
+        ptr('pre_conf'), ptr('pre_yx'), ptr('pre_cell'), o['n_pre'].data_ptr(),
         o['conf'].data_ptr(), o['yx'].data_ptr(), o['keep_idx'].data_ptr(), o['n_out'].data_ptr(),
         _stream()))
     return o

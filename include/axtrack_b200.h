@@ -135,7 +135,9 @@ int axb_cost_matrix_host(axb_ctx* ctx, const uint8_t* mask_host, int H, int W,
  * Outputs (cap = row pitch; AXB_ERR_CAPACITY is set if a frame has more candidates):
  *   pre_*     the stitched pre-NMS frame detections in the reference's concat order
  *             (tile-major; inside a tile conf ascending): conf [F,cap], frame coords
- *             [F,cap,2] as (y, x) -- the row layout axb_cost_matrix_batch reads --, tile [F,cap]
+ *             [F,cap,2] as (y, x) -- the row layout axb_cost_matrix_batch reads --, cell [F,cap] = the
+ *             grid cell the candidate came from, tile*Sx*Sy + ix*Sy + iy (the reference names a
+ *             tile's detections Axon_### by their rank in this order, AxonDetections.py:222-235)
  *   n_pre     int32 [F]
  *   conf/yx   NMS survivors in conf-descending order ([F,cap], [F,cap,2] rows (y, x));
  *             keep_idx = their pre-NMS indices ("survivor indices")
@@ -145,7 +147,7 @@ int axb_cost_matrix_host(axb_ctx* ctx, const uint8_t* mask_host, int H, int W,
 int axb_decode_nms(axb_ctx* ctx, const float* Y_dev, const int32_t* tile_yx_dev,
                    int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist,
                    int cap,
-                   float* pre_conf_dev, int32_t* pre_yx_dev, int32_t* pre_tile_dev, int32_t* n_pre_dev,
+                   float* pre_conf_dev, int32_t* pre_yx_dev, int32_t* pre_cell_dev, int32_t* n_pre_dev,
                    float* conf_dev, int32_t* yx_dev, int32_t* keep_idx_dev, int32_t* n_out_dev,
                    void* stream);
 
@@ -157,7 +159,7 @@ int axb_decode_nms(axb_ctx* ctx, const float* Y_dev, const int32_t* tile_yx_dev,
 int axb_decode_nms_host(axb_ctx* ctx, const float* Y_host, const int32_t* tile_yx_host,
                         int F, int ntiles, int Sx, int Sy, int tilesize, float conf_thr, int nms_dist,
                         int cap,
-                        float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_tile_host, int32_t* n_pre_host,
+                        float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_cell_host, int32_t* n_pre_host,
                         float* conf_host, int32_t* yx_host, int32_t* keep_idx_host, int32_t* n_out_host);
 
 /* ---- status ----------------------------------------------------------------------------

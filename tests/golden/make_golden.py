@@ -45,8 +45,11 @@ def gold_decode_nms(seed, H, W, n):
         hit = np.nonzero((pre[:, 0] == c) & (pre[:, 1] == x) & (pre[:, 2] == y))[0]
         assert len(hit) == 1
         keep.append(hit[0])
+    # the tile-wise frames (_pandas_tiled_dets, AxonDetections.py:131-132): tile, Axon_### label, conf, x, y
+    tl = np.array([[i, int(lbl.split('_')[1]), float(r.conf), float(r.anchor_x), float(r.anchor_y)]
+                   for i, df in enumerate(tiled) for lbl, r in df.iterrows()], np.float64).reshape(-1, 5)
     out = os.path.join(HERE, f'decode_nms_s{seed}.npz')
-    np.savez_compressed(out, Y=Y, tile_yx=synth.tile_table(H, W), H=H, W=W, conf_thr=float(thr),
+    np.savez_compressed(out, tiled=tl, Y=Y, tile_yx=synth.tile_table(H, W), H=H, W=W, conf_thr=float(thr),
                         nms_dist=int(ad.nms_min_dist), tilesize=int(ad.tilesize),
                         pre_conf=pre[:, 0].astype(np.float32), pre_x=pre[:, 1].astype(np.int64),
                         pre_y=pre[:, 2].astype(np.int64), conf=post[:, 0].astype(np.float32),
