@@ -25,8 +25,9 @@ constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHas
 constexpr int kK2Threads = 256;       // one CTA (8 warps) per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
 // fast kernel (level 0 only): 3 CTAs per SM
-constexpr int kFastQCap = 768;        // frontier entries per buffer in shared memory
-constexpr int kFastGQCap = 16384;     // per-CTA global overflow entries per buffer
+constexpr int kFastThreads = 128;     // fast kernel: one CTA (4 warps) per source search, one thread per frontier entry
+constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory
+constexpr int kFastGQCap = 4096;      // per-CTA global overflow entries per buffer
 constexpr int kFastCtasPerSm = 3;
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
@@ -54,12 +55,12 @@ struct K2Params {
 };
 
 inline size_t k2_fast_smem_bytes(int max_px) {
-    return ((size_t)(max_px + 1) * kRowWords + 2 * kFastQCap + kHashSize) * sizeof(uint32_t);
+    return ((size_t)((max_px + 3) / 4 + 1) * 128 + 4 * kFastQCap + kHashSize) * sizeof(uint32_t);
 }
 inline size_t k2_gen_smem_bytes(int max_px) {
     return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
 }
-constexpr size_t kFastScratchWords = (size_t)kCandCap + 2 * (size_t)kFastGQCap;
+constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
 
 void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,

@@ -182,8 +182,8 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
     const uint32_t lt = lanemask_lt();
     const int RW = p.max_px;
     const int nwords = (RW + 1) * kRowWords;
-    constexpr int QCAP = GEN ? kGenQCap : kFastQCap;
-    constexpr int GQCAP = GEN ? kGCap : kFastGQCap;
+    constexpr int QCAP = kGenQCap;
+    constexpr int GQCAP = kGCap;
 
     uint32_t* const OF = smem;
     uint32_t* const OB = OF + (GEN ? nwords : 0);
@@ -306,59 +306,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
             const int dcx = dir == 1 ? -1 : dir == 2 ? 1 : 0;
             // Expanded cells sit at hop <= max_px-1, so every neighbour lies inside the diamond: no
             // bound check; pixels outside the image were staged as closed.
-            if (!GEN) {
-                // ---- level 0 only ---------------------------------------------------------
-                int cur_n = 1, j = 0, step = 0;
-                bool hit = false, overflow = false;
-                while (cur_n > 0 && unsettled > 0) {
-                    if (j >= RW) { hit = true; break; }               // cells at hop == max_px exist
-                    if (cur_n > QCAP + GQCAP) { overflow = true; break; }
-                    const uint32_t* const qcur = q0 + (step & 1) * QCAP;
-                    uint32_t* const qnxt = q0 + ((step + 1) & 1) * QCAP;
-                    const uint32_t* const gcur = gq0 + (size_t)(step & 1) * GQCAP;
-                    uint32_t* const gnxt = gq0 + (size_t)((step + 1) & 1) * GQCAP;
-                    int* const cnt_nxt = &ctl.cnt[(step + 1) % 3];
-                    int* const set_nxt = &ctl.settled[(step + 1) % 3];
-                    const int ntask = cur_n * 4;
-                    for (int base = (tid & ~31); base < ntask; base += NT) {
-                        const int i = (base + lane) >> 2;
-                        bool got = false;
-                        int idx = 0;
-                        uint32_t ne = 0;
-                        if (i < cur_n) {
-                            const uint32_t e = i < QCAP ? qcur[i] : gcur[i - QCAP];
-                            const int ndy = (int)(e >> 11) - 512 + ddy, ncx = (int)(e & 2047u) - 512 + dcx;
-                            idx = fold_index(ndy, ncx, RW);
-                            ne = pack_cell(ndy, ncx);
-                            const int pw = phys_word(idx);
-                            const uint32_t bit = 1u << (idx & 31);
-                            if (OF[pw] & bit) got = (atomicAnd(&OF[pw], ~bit) & bit) != 0;
-                        }
-                        const uint32_t bal = __ballot_sync(kFull, got);
-                        if (bal) {
-                            int pos = 0;
-                            if (lane == 0) pos = atomicAdd(cnt_nxt, __popc(bal));
-                            pos = __shfl_sync(kFull, pos, 0);
-                            if (got) {
-                                const int slot = pos + __popc(bal & lt);
-                                if (slot < QCAP) qnxt[slot] = ne;
-                                else if (slot - QCAP < GQCAP) gnxt[slot - QCAP] = ne;
-                                if (j + 1 < RW) {
-                                    const int ns = probe_settle(p, hash, cand, ch, (uint32_t)idx, 0, j + 1);
-                                    if (ns) atomicAdd(set_nxt, ns);
-                                }
-                            }
-                        }
-                    }
-                    __syncthreads();
-                    cur_n = *cnt_nxt;
-                    unsettled -= *set_nxt;
-                    if (tid == 0) { ctl.cnt[step % 3] = 0; ctl.settled[step % 3] = 0; }
-                    ++step;
-                    ++j;
-                }
-                if (overflow || (!hit && unsettled > 0)) return true;     // level 0 cannot answer: defer
-            } else {
+            {
                 // ---- all levels -------------------------------------------------------------
                 int n_seeds = 1;
                 for (int k = 0; k <= RW && n_seeds > 0 && unsettled > 0; ++k) {
@@ -462,22 +410,6 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
 
 }  // namespace
 
-__global__ void __launch_bounds__(kK2Threads, kFastCtasPerSm) k2_fast_kernel(const K2Params p) {
-    extern __shared__ __align__(16) uint32_t smem[];
-    __shared__ Ctl ctl;
-    uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
-    const int total = p.work_prefix[p.n_pairs];
-    for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[0], 1);
-        __syncthreads();
-        const int item = ctl.item;
-        if (item >= total) break;
-        const bool defer = run_item<false, kK2Threads>(p, item, smem, gscr, ctl);
-        if (defer && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
-    }
-}
-
 __global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
@@ -566,16 +498,6 @@ __global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __re
 void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
                     int* next_same, int* counters, cudaStream_t stream) {
     k2_prep_kernel<<<1, 1024, 0, stream>>>(pairs, n_pairs, work_prefix, all_prefix, next_same, counters);
-}
-
-void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_fast_smem_bytes(AXB_MAX_PX));
-        cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        attr_set = true;
-    }
-    k2_fast_kernel<<<grid, kK2Threads, k2_fast_smem_bytes(p.max_px), stream>>>(p);
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {

@@ -23,3 +23,13 @@ for i in range(6):
     e0.record(); ops.cost_matrix_batch(bits, wl['W'], det['yx'].view(-1, 2), pairs, 500, want_cost=False, out=outb, pairs_dev=pd); e1.record()
     torch.cuda.synchronize(); ms.append(e0.elapsed_time(e1))
 print(sys.argv[1] if len(sys.argv) > 1 else 'default', 'K2 ms', ['%.2f' % m for m in ms], 'pairs', len(keys), 'sources', int(n_out[:-1].sum()), 'checksum', int(outb[0].sum()), int(outb[1].sum()))
+if len(sys.argv) > 1 and 'timing' in sys.argv[1]:
+    import ctypes
+    L = _lib.load()
+    buf = (ctypes.c_ulonglong * 8)()
+    L.axb_dbg_fetch(buf, 1)
+    ops.cost_matrix_batch(bits, wl['W'], det['yx'].view(-1, 2), pairs, 500, want_cost=False, out=outb, pairs_dev=pd); torch.cuda.synchronize()
+    L.axb_dbg_fetch(buf, 1)
+    b = list(buf)
+    print('timing: items', b[4], 'waves/item %.1f' % (b[3] / max(b[4], 1)), 'entries/wave %.1f' % (b[5] / max(b[3], 1)),
+          'cycles/item: setup %.0f staging %.0f waves %.0f' % (b[0] / b[4], b[1] / b[4], b[2] / b[4]), 'cycles/wave %.0f' % (b[2] / max(b[3], 1)), 'warp0 body %.0f barrier+lds %.0f' % (b[6] / max(b[3], 1), b[7] / max(b[3], 1)))
