@@ -24,6 +24,8 @@ struct axb_ctx {
     int* counters = nullptr;
     int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;   // [work | all | next] x prefix_cap
     int* gen_list = nullptr;          size_t gen_list_bytes = 0;
+    int* dense_list = nullptr;        size_t dense_list_bytes = 0;
+    uint32_t* k2_tiles = nullptr;     size_t k2_tiles_bytes = 0;       // 8x4-pixel tile words of the masks of the current call
     // K1
     uint8_t* k1_scratch = nullptr;    size_t k1_scratch_bytes = 0;
     // staging for the single-pair and host entry points
@@ -63,7 +65,7 @@ int grow(axb_ctx* c, T** ptr, size_t* have, size_t need) {
 
 int ensure_k2(axb_ctx* c, int n_pairs, int total_src) {
     if (!c->k2_fast_scratch) {
-        c->k2_fast_ctas = c->num_sms * axb::kFastCtasPerSm;
+        c->k2_fast_ctas = c->num_sms * std::max(axb::kFastCtasPerSm, axb::kSparseCtasPerSm);
         AXB_CUDA(c, cudaMalloc((void**)&c->k2_fast_scratch, (size_t)c->k2_fast_ctas * axb::kFastScratchWords * sizeof(uint32_t)));
     }
     if (!c->k2_gen_scratch) {
@@ -77,6 +79,8 @@ int ensure_k2(axb_ctx* c, int n_pairs, int total_src) {
         c->prefix_cap = std::max(n_pairs + 1, 1024) * 2;
         AXB_CUDA(c, cudaMalloc((void**)&c->prefix_dev, 3 * (size_t)c->prefix_cap * sizeof(int)));
     }
+    int rc = grow(c, &c->dense_list, &c->dense_list_bytes, (size_t)std::max(total_src, 1) * sizeof(int));
+    if (rc != AXB_OK) return rc;
     return grow(c, &c->gen_list, &c->gen_list_bytes, (size_t)std::max(total_src, 1) * sizeof(int));
 }
 
@@ -114,7 +118,7 @@ void axb_destroy(axb_ctx* c) {
     cudaDeviceSynchronize();
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
-    cudaFree(c->gen_list); cudaFree(c->k1_scratch);
+    cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
     cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -161,21 +165,27 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     cudaStream_t s = (cudaStream_t)stream;
     int rc = ensure_k2(c, n_pairs, total_src);
     if (rc != AXB_OK) return rc;
+    const int Wp = (W + 31) / 32, TH = (H + 3) / 4;
+    rc = grow(c, &c->k2_tiles, &c->k2_tiles_bytes, (size_t)n_masks * TH * Wp * 4 * sizeof(uint32_t));
+    if (rc != AXB_OK) return rc;
+    axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
     int* const work_prefix = c->prefix_dev;
     int* const all_prefix = c->prefix_dev + c->prefix_cap;
     int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
     axb::launch_k2_prep(pairs_dev, n_pairs, work_prefix, all_prefix, next_same, c->counters, s);
     c->last_n_pairs = n_pairs;
     axb::K2Params p;
-    p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = (W + 31) / 32;
+    p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = Wp;
+    p.mask_tiles = c->k2_tiles; p.TH = TH; p.TWp = 4 * Wp;
     p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs;
     p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
     p.max_px = max_px; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
-    p.counters = c->counters; p.gen_list = c->gen_list; p.err_key = c->status_dev;
-    axb::launch_k2_fast(p, std::max(1, std::min(c->k2_fast_ctas, total_src)), s);
+    p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
+    axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
+    axb::launch_k2_fast(p, std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src)), s);
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
-    c->launches += 3;
+    c->launches += 5;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;
 }

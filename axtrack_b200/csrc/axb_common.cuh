@@ -25,10 +25,17 @@ constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHas
 constexpr int kK2Threads = 256;       // one CTA (8 warps) per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
 // fast kernel (level 0 only): 3 CTAs per SM
-constexpr int kFastThreads = 128;     // fast kernel: one CTA (4 warps) per source search, one thread per frontier entry
+constexpr int kFastThreads = 128;     // fast kernels: one CTA (4 warps) per source search, one thread per frontier entry
+constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entries per buffer
+// dense window (every tile word of the folded diamond, 64.5 KB): 3 CTAs per SM
 constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory
-constexpr int kFastGQCap = 4096;      // per-CTA global overflow entries per buffer
 constexpr int kFastCtasPerSm = 3;
+// sparse window (only the non-zero tile words + a presence/base table): 8 CTAs per SM
+constexpr int kSparseWords = 4416;    // non-zero tile words a sparse window can hold (17.25 KB)
+constexpr int kSparseQCap = 256;
+constexpr int kSparseHash = 512;
+constexpr int kSparseHashMaxLoad = 320;
+constexpr int kSparseCtasPerSm = 8;
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
@@ -37,6 +44,8 @@ constexpr uint32_t kEmpty = 0xFFFFFFFFu;
 struct K2Params {
     const uint32_t* mask_bits;   // [n_masks][H][Wp]
     int H, W, Wp;
+    const uint32_t* mask_tiles;  // [n_masks][TH][TWp] 8x4-pixel tile words (bit = (y&3)*8 + (x&7)), built per call
+    int TH, TWp;                 // TH = ceil(H/4), TWp = 4*Wp
     const int32_t* dets_yx;      // [n][2] (y, x)
     const axb_pair_desc* pairs;  // device
     int n_pairs;
@@ -49,13 +58,18 @@ struct K2Params {
     float* wcost;
     uint32_t* fast_scratch;      // per fast CTA: kCandCap + 2*kFastGQCap words
     uint32_t* gen_scratch;       // per general CTA: kCandCap + 4*kGCap words
-    int* counters;               // [0] fast ticket, [1] general list length, [2] general ticket
+    int* counters;               // [0] sparse ticket, [1] general list length, [2] general ticket, [3] dense list length, [4] dense ticket
     int* gen_list;               // work items deferred to the general kernel
+    int* dense_list;             // work items whose window does not fit the sparse layout
     unsigned long long* err_key; // atomicMin: (item in reference order << 26 | target << 2 | code)
 };
 
-inline size_t k2_fast_smem_bytes(int max_px) {
-    return ((size_t)((max_px + 3) / 4 + 1) * 128 + 4 * kFastQCap + kHashSize) * sizeof(uint32_t);
+inline int k2_tile_rows(int max_px) { return (max_px + 3) / 4 + 1; }
+inline size_t k2_fast_smem_bytes(int max_px) {      // dense window + queues + hash
+    return ((size_t)k2_tile_rows(max_px) * 128 + 4 * kFastQCap + kHashSize) * sizeof(uint32_t);
+}
+inline size_t k2_sparse_smem_bytes(int max_px) {    // packed words + (presence, base) per 32 tile columns + queues + hash
+    return ((size_t)kSparseWords + (size_t)k2_tile_rows(max_px) * 8 + 4 * kSparseQCap + kSparseHash) * sizeof(uint32_t);
 }
 inline size_t k2_gen_smem_bytes(int max_px) {
     return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
@@ -65,6 +79,8 @@ constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
 
 void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
                     int* next_same, int* counters, cudaStream_t stream);
+void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);
+void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);

@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __re
     __shared__ int s_warp[2][32];
     const int tid = threadIdx.x;
     int* const prev = work_prefix;            // scratch until the scan overwrites it
-    if (tid < 3) counters[tid] = 0;
+    if (tid < 8) counters[tid] = 0;
     for (int i = tid; i < n_pairs; i += blockDim.x) {
         const axb_pair_desc a = pairs[i];
         int pv = -1, nx = -1;

@@ -1,28 +1,34 @@
-// K2 fast kernel (v5) -- level-0 bounded multi-target search with WORD-PARALLEL wavefronts (sm_100a).
+// K2 fast kernels (v8) -- level-0 bounded multi-target search with word-parallel wavefronts (sm_100a).
 //
-// Same contract as the per-cell kernel it replaces (see axb_search.cu header and DESIGN.md "K2
-// semantics"): one search per SOURCE detection answers every in-range target of the source's
-// chain of frame pairs; replaces pyastar2d/src/cpp/astar.cpp:46-172 driven by
-// axtrack/AxonDetections.py:553-579,600-629 for every source whose mask component reaches hop
-// max_px or contains all its in-range targets.  Sources it cannot answer (level 0 exhausted
-// with targets open) are deferred to k2_general_kernel.
+// Contract (axb_search.cu header, DESIGN.md "K2 semantics"): one search per SOURCE detection
+// answers every in-range target of the source's chain of frame pairs; replaces
+// pyastar2d/src/cpp/astar.cpp:46-172 driven by axtrack/AxonDetections.py:553-579,600-629 for every
+// source whose mask component reaches hop max_px or contains all its in-range targets.  Sources
+// level 0 cannot answer are deferred to k2_general_kernel.
 //
-// What changed against v4 (profiles/r01a_*): v4 spent ~230 warp instructions per warp per
-// wavefront on one lane per (frontier cell, direction) and was issue bound.  Here the window
-// bitmap is stored as 8x4-pixel TILE WORDS (bit = (y&3)*8 + (x&7)); a frontier entry is a
-// (tile word, 32 frontier bits) pair and ONE thread expands all cells of the word with five
-// shift/mask candidates (same word, left, right, up, down word) and at most five shared-memory
-// atomicAnd claims.  A corridor wavefront of ~15 cells is 3-5 entries whatever its orientation.
+// Window = the L1 ball of radius RW = max_px around the source as 8x4-pixel TILE WORDS
+// (bit = (y&3)*8 + (x&7)), read from the tiled copy of the packed mask that k2_tile_mask_kernel
+// builds once per call.  Tile rows of 4 image rows are aligned to (sy & ~3), tile columns of 8
+// pixels to (sx & ~31), and the diamond is FOLDED on a circle of 128 tile columns: tile rows
+// tr <= 0 live in folded row tr+NR-1 with the source's aligned column at tile column 64, tile
+// rows tr >= 1 in folded row tr-1 with it at tile column 0; NR = ceil(RW/4)+1.  The half widths of
+// the two tile rows sharing a folded row add up to <= RW-1, so their pixels never meet on the
+// 1024 px circle.  Only in-diamond mask pixels are staged as open and cells at hop RW are never
+// expanded, so every candidate bit of an expansion is a true 4-neighbour: no bound checks.
+//   key of a tile word = half << 15 | folded row << 7 | tile column.
 //
-// Window layout.  The L1 ball of radius RW = max_px around the source, in tile rows of 4 image
-// rows aligned to (sy & ~3) and tile columns of 8 pixels aligned to (sx & ~31), FOLDED on a
-// circle of 128 tile columns (1024 px): tile rows tr <= 0 live in folded row tr+NR-1 with the
-// source's aligned column at tile column 64, tile rows tr >= 1 live in folded row tr-1 with it
-// at tile column 0; NR = ceil(RW/4)+1.  The half widths of the two tile rows that share a folded
-// row add up to <= RW-1, so their pixel ranges never overlap on the 1024 px circle.  Only
-// in-diamond, in-image mask pixels are staged as open, and cells at hop RW are never expanded,
-// so every candidate bit of an expansion is a true 4-neighbour inside the same half: no bound
-// checks in the wavefront.  64.5 KB at max_px = 500 -> 3 CTAs per SM.
+// A frontier entry is (tile word key, 32 frontier bits); ONE thread expands all its cells with
+// five shift/mask candidates (word itself, right, left, below, above) and at most five
+// predicated shared-memory atomicAnd claims.  Each warp appends its claims to its own segment
+// of the next frontier (ballot ranks, no counter atomics); one __syncthreads per wavefront.
+//
+// Two instantiations of the same search:
+//   k2_sparse_kernel  window = only the NON-ZERO tile words (<= kSparseWords) + a (presence
+//                     bits, base index) pair per 32 tile columns: ~28 KB per search -> 8 CTAs
+//                     per SM.  A search is ~max_px dependent wavefronts (latency bound), so the
+//                     throughput comes from the number of resident searches.
+//   k2_fast_kernel    dense window (64.5 KB, 3 CTAs per SM) for the sources whose window has
+//                     more non-zero tile words than the sparse layout holds (dense masks).
 #include "axb_common.cuh"
 
 namespace axb {
@@ -32,41 +38,29 @@ namespace {
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kTC = 128;                  // tile columns per folded row
 
-__device__ __forceinline__ uint32_t span_mask(int a, int b) {
-    a = a < 0 ? 0 : a;
-    b = b > 31 ? 31 : b;
-    if (a > b) return 0u;
-    return (0xFFFFFFFFu >> (31 - b)) & (0xFFFFFFFFu << a);
-}
-
 __device__ __forceinline__ uint32_t lanemask_lt() {
     uint32_t m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
 }
 
-// meta of a tile word: half << 15 | shared-memory word index, where the word index is
-// folded row << 7 | physical column and the 128 words of folded row fr are rotated by kRot*fr
-// (physical column = (tile column + kRot*fr) & 127) so that vertical runs of tile words spread
-// over the banks.
-constexpr int kRot = 0;
-__device__ __forceinline__ uint32_t make_meta(int half, int fr, int col) {
-    return ((uint32_t)half << 15) | ((uint32_t)fr << 7) | (uint32_t)((col + kRot * fr) & (kTC - 1));
+__device__ __forceinline__ uint32_t make_key(int half, int fr, int col) {
+    return ((uint32_t)half << 15) | ((uint32_t)fr << 7) | (uint32_t)col;
 }
-__device__ __forceinline__ int phys_word(uint32_t meta) { return (int)(meta & 0x7FFFu); }
-// cell (dy, dx) relative to the source -> meta and bit of its tile word
-__device__ __forceinline__ uint32_t cell_meta(int dy, int dx, int oy, int ox, int NR, int& bit) {
+// cell (dy, dx) relative to the source -> key and bit of its tile word
+__device__ __forceinline__ uint32_t cell_key(int dy, int dx, int oy, int ox, int NR, int& bit) {
     const int cy = dy + oy, cx = dx + ox;
     const int tr = cy >> 2;
     const int half = tr > 0;
     const int fr = half ? tr - 1 : tr + NR - 1;
     const int col = ((cx >> 3) + (half ? 0 : 64)) & (kTC - 1);
     bit = ((cy & 3) << 3) | (cx & 7);
-    return make_meta(half, fr, col);
+    return make_key(half, fr, col);
 }
 
-__device__ __forceinline__ uint32_t hash_slot(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
-static_assert(kHashSize == 1024, "hash_slot keeps 10 bits");
+template <int HASH> __device__ __forceinline__ uint32_t hash_slot(uint32_t key);
+template <> __device__ __forceinline__ uint32_t hash_slot<1024>(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
+template <> __device__ __forceinline__ uint32_t hash_slot<512>(uint32_t key) { return (key * 0x9E3779B1u) >> 23; }
 static_assert(kCandCap <= 2048, "hash entries keep 11 bits of candidate slot");
 
 struct Chain {
@@ -84,85 +78,91 @@ struct __align__(16) Ctl {
     Chain ch;
     int ncand;
     int item;
+    int alloc;         // sparse: packed tile words allocated so far
 };
 
 struct Win {
-    const uint32_t* mbits;
-    int H, W, Wp, sy, sx, RW, NR, oy, ox, iw0;
+    const uint32_t* tiles;       // tiled mask of this source's mask
+    int TH, TWp, ty0, tx0;       // tile grid, global tile of the window's (tile row 0, tile column 0)
+    int RW, NR, oy, ox;
 };
 
-// one aligned word of the packed mask of image row y, restricted to the diamond row span
-__device__ __forceinline__ uint32_t row_word(const Win& w, int dy, int iw) {
-    const int hw = w.RW - abs(dy);
-    const int y = w.sy + dy;
-    if (hw < 0 || y < 0 || y >= w.H || iw < 0 || iw >= w.Wp) return 0u;
-    const int xlo = max(0, w.sx - hw), xhi = min(w.W - 1, w.sx + hw);
-    const uint32_t valid = span_mask(xlo - 32 * iw, xhi - 32 * iw);
-    if (!valid) return 0u;
-    return __ldg(w.mbits + (size_t)y * w.Wp + iw) & valid;
+// Tile word (tile row tr, tile column tc of the window) with the pixels outside the diamond
+// cleared.  hw_in / hw_out: half widths of the narrowest / widest image row of the tile row.
+__device__ __forceinline__ uint32_t window_tile(const Win& w, int tr, int tc, int hw_in, int hw_out) {
+    const int x0 = 8 * tc - w.ox;                       // dx of the tile's first pixel
+    if (x0 + 7 < -hw_out || x0 > hw_out) return 0u;
+    const int ty = w.ty0 + tr, tx = w.tx0 + tc;
+    if (ty < 0 || ty >= w.TH || tx < 0 || tx >= w.TWp) return 0u;
+    uint32_t m = 0xFFFFFFFFu;
+    if (x0 < -hw_in || x0 + 7 > hw_in) {                // the diamond edge crosses the tile
+        m = 0u;
+        const int dy0 = 4 * tr - w.oy;
+        #pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int hw = w.RW - abs(dy0 + r);
+            const int lo = max(-hw - x0, 0), hi = min(hw - x0, 7);
+            if (hw >= 0 && lo <= hi) m |= (((0xFFu >> (7 - hi)) & (0xFFu << lo)) & 0xFFu) << (8 * r);
+        }
+        if (m == 0u) return 0u;
+    }
+    return __ldg(w.tiles + (size_t)ty * w.TWp + tx) & m;
 }
 
-// the four tile words (tile columns 4q..4q+3 of the quad) of tile row tr and image word iw
-__device__ __forceinline__ void quad_tiles(const Win& w, int tr, int iw, uint32_t t[4]) {
-    const int dy0 = 4 * tr - w.oy;
-    const uint32_t r0 = row_word(w, dy0, iw), r1 = row_word(w, dy0 + 1, iw);
-    const uint32_t r2 = row_word(w, dy0 + 2, iw), r3 = row_word(w, dy0 + 3, iw);
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const uint32_t lo = __byte_perm(r0, r1, k | ((4 + k) << 4));
-        const uint32_t hi = __byte_perm(r2, r3, k | ((4 + k) << 4));
-        t[k] |= __byte_perm(lo, hi, 0x5410);
+// tile word of folded row fr, folded column col: the upper-half and the lower-half candidates
+__device__ __forceinline__ uint32_t folded_tile(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l) {
+    const int tr_u = fr - w.NR + 1;
+    uint32_t t = window_tile(w, tr_u, col - 64, hwi_u, hwo_u);
+    if (col < 8) t |= window_tile(w, tr_u, col + 64, hwi_u, hwo_u);
+    if (fr + 1 <= w.NR - 1) {
+        if (col < 72) t |= window_tile(w, fr + 1, col, hwi_l, hwo_l);
+        if (col >= 56) t |= window_tile(w, fr + 1, col - 128, hwi_l, hwo_l);
     }
+    return t;
 }
 
-// Stage the folded window: one warp per folded row, lane = quad of 4 tile columns = one aligned
-// word of the packed mask per image row.
-template <int NT>
-__device__ __forceinline__ void stage_window(const Win& w, uint32_t* OF) {
-    const int lane = threadIdx.x & 31;
-    for (int fr = threadIdx.x >> 5; fr < w.NR; fr += NT / 32) {
-        uint32_t t[4] = {0u, 0u, 0u, 0u};
-        {   // upper half: tile row fr-NR+1 <= 0, quad q holds cx in [32(q-16), 32(q-16)+31]
-            const int tr = fr - w.NR + 1;
-            quad_tiles(w, tr, w.iw0 - 16 + lane, t);
-            if (lane == 0) quad_tiles(w, tr, w.iw0 + 16, t);
-        }
-        if (fr + 1 <= w.NR - 1) {   // lower half: tile row fr+1, quad q holds cx in [32q, ..] (q<16) or [32(q-32), ..]
-            const int tr = fr + 1;
-            quad_tiles(w, tr, w.iw0 + (lane < 16 ? lane : lane - 32), t);
-            if (lane == 16) quad_tiles(w, tr, w.iw0 + 16, t);
-        }
-        static_assert(kRot == 0, "the quad is stored with one 16-byte store");
-        *reinterpret_cast<uint4*>(OF + fr * kTC + 4 * lane) = make_uint4(t[0], t[1], t[2], t[3]);
-    }
-}
-
-// Slow path of the target probe: the hash slot of tile word `key` is occupied.  The cells
-// `claimed` of the word were reached with j mask pixels on the path (hop j, path length j+1).
-__device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash, const uint32_t* cand,
-                                         const Chain& ch, uint32_t key, uint32_t claimed, int j) {
-    int n = 0;
-    uint32_t h = hash_slot(key);
-    for (;;) {
-        const uint32_t e = hash[h];
-        if (e == kEmpty) break;
-        if ((e >> 16) == key && ((claimed >> ((e >> 11) & 31u)) & 1u)) {
-            const uint32_t c = cand[e & 0x7FFu];
-            const long long o = ch.orow[c >> 30] + (long long)(c & 0x3FFFFFFFu);
-            p.path_len[o] = j + 1;
-            p.unreachable[o] = 0;
-            if (p.wcost) p.wcost[o] = (float)j;
-            ++n;
-        }
-        h = (h + 1) & (kHashSize - 1);
-    }
-    return n;
+__device__ __forceinline__ void row_half_widths(const Win& w, int tr, int& hw_in, int& hw_out) {
+    const int a = 4 * tr - w.oy, b = a + 3;             // dy of the first / last image row
+    const int far = max(abs(a), abs(b));
+    const int near = (a <= 0 && b >= 0) ? 0 : min(abs(a), abs(b));
+    hw_in = w.RW - far;                                 // may be negative: no tile is interior
+    hw_out = w.RW - near;
 }
 
 }  // namespace
 
+// Tiled copy of the bit-packed mask: one thread per (tile row, packed word) turns four row words
+// into the four 8x4 tile words of the same 32 pixels (byte k of the four rows).
+__global__ void __launch_bounds__(256) k2_tile_mask_kernel(const uint32_t* __restrict__ bits, int n_masks, int H, int Wp,
+                                                            uint32_t* __restrict__ tiles) {
+    const int TH = (H + 3) / 4;
+    const long long n = (long long)n_masks * TH * Wp;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int iw = (int)(i % Wp);
+        const long long rest = i / Wp;
+        const int ty = (int)(rest % TH);
+        const int m = (int)(rest / TH);
+        const uint32_t* src = bits + ((size_t)m * H + 4 * (size_t)ty) * Wp + iw;
+        uint32_t r[4];
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] = 4 * ty + k < H ? __ldg(src + (size_t)k * Wp) : 0u;
+        uint4 t;
+        uint32_t* tp = &t.x;
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t lo = __byte_perm(r[0], r[1], k | ((4 + k) << 4));
+            const uint32_t hi = __byte_perm(r[2], r[3], k | ((4 + k) << 4));
+            tp[k] = __byte_perm(lo, hi, 0x5410);
+        }
+        *reinterpret_cast<uint4*>(tiles + ((size_t)m * TH + ty) * (4 * (size_t)Wp) + 4 * (size_t)iw) = t;
+    }
+}
 
-
+void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream) {
+    const long long n = (long long)n_masks * ((H + 3) / 4) * Wp;
+    const int grid = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+    k2_tile_mask_kernel<<<grid > 0 ? grid : 1, 256, 0, stream>>>(mask_bits, n_masks, H, Wp, tiles);
+}
 
 #ifdef AXB_TIMING
 __device__ unsigned long long g_dbg[8];   // cycles: [0] setup+candidates [1] staging [2] waves; [3] #waves [4] #items [5] entries [6] warp-0 wave body [7] barrier
@@ -176,20 +176,33 @@ __device__ unsigned long long g_dbg[8];   // cycles: [0] setup+candidates [1] st
 namespace {
 
 constexpr int kNW = kFastThreads / 32;            // warps per search
-constexpr int kSeg = kFastQCap / kNW;             // shared-memory frontier entries per warp per buffer
 constexpr int kGSeg = kFastGQCap / kNW;           // global overflow entries per warp per buffer
 static_assert(kNW == 4, "Ctl::wc holds one word per warp in one 16-byte row");
-static_assert(kSeg + kGSeg < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
+
+template <bool SPARSE> struct Cfg;
+template <> struct Cfg<false> {
+    static constexpr int kQCap = kFastQCap, kSeg = kFastQCap / kNW, kHash = kHashSize, kMaxLoad = kHashMaxLoad;
+};
+template <> struct Cfg<true> {
+    static constexpr int kQCap = kSparseQCap, kSeg = kSparseQCap / kNW, kHash = kSparseHash, kMaxLoad = kSparseHashMaxLoad;
+};
+static_assert(kFastQCap / kNW + kGSeg < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // Shared-memory operations of the wavefront as predicated PTX, so that the five directions of an
-// entry issue back to back instead of through five branches.
+// entry issue back to back.
 // value at shared address `a`, or 0 when want == 0 (the address may then be invalid)
 __device__ __forceinline__ uint32_t lds_if(uint32_t a, uint32_t want) {
     uint32_t v;
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\tmov.u32 %0, 0;\n\t@p ld.shared.u32 %0, [%1];\n\t}"
                  : "=r"(v) : "r"(a), "r"(want) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint2 lds64_if(uint32_t a, uint32_t want) {
+    uint2 v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\tmov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\t@p ld.shared.v2.u32 {%0, %1}, [%2];\n\t}"
+                 : "=r"(v.x), "=r"(v.y) : "r"(a), "r"(want) : "memory");
     return v;
 }
 // clear the bits `o` of the word at shared address `a`; returns those of them this thread cleared
@@ -205,21 +218,93 @@ __device__ __forceinline__ void sts64_if(uint32_t a, uint32_t x, uint32_t y, uin
                  :: "r"(a), "r"(x), "r"(y), "r"(want) : "memory");
 }
 
-// One work item = one source of a chain leader, processed by the whole CTA.  Returns true when
-// the item must be redone by the general kernel.  All control flow is CTA-uniform.
-__device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
+// Slow path of the target probe: the hash slot of tile word `key` is occupied.  The cells
+// `claimed` of the word were reached with j mask pixels on the path (hop j, path length j+1).
+template <int HASH>
+__device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash, const uint32_t* cand,
+                                         const Chain& ch, uint32_t key, uint32_t claimed, int j) {
+    int n = 0;
+    uint32_t h = hash_slot<HASH>(key);
+    for (;;) {
+        const uint32_t e = hash[h];
+        if (e == kEmpty) break;
+        if ((e >> 16) == key && ((claimed >> ((e >> 11) & 31u)) & 1u)) {
+            const uint32_t c = cand[e & 0x7FFu];
+            const long long o = ch.orow[c >> 30] + (long long)(c & 0x3FFFFFFFu);
+            p.path_len[o] = j + 1;
+            p.unreachable[o] = 0;
+            if (p.wcost) p.wcost[o] = (float)j;
+            ++n;
+        }
+        h = (h + 1) & (HASH - 1);
+    }
+    return n;
+}
+
+// Stage the folded window from the tiled mask: one warp per folded row, four passes of 32 tile
+// columns, lane = tile column.  Dense: WIN[fr*128 + col].  Sparse: the non-zero words of the 32
+// columns are packed behind each other, PB[fr*4 + g] = (presence bits, index of the first one);
+// groups are allocated in any order (one atomicAdd per folded row).  Returns via ctl.alloc.
+template <bool SPARSE>
+__device__ __forceinline__ void stage_window(const Win& w, uint32_t* WIN, uint2* PB, Ctl& ctl) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = lanemask_lt();
+    for (int fr = threadIdx.x >> 5; fr < w.NR; fr += kNW) {
+        int hwi_u, hwo_u, hwi_l, hwo_l;
+        row_half_widths(w, fr - w.NR + 1, hwi_u, hwo_u);
+        row_half_widths(w, fr + 1, hwi_l, hwo_l);
+        uint32_t t[4];
+        #pragma unroll
+        for (int g = 0; g < 4; ++g) t[g] = folded_tile(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l);
+        if (!SPARSE) {
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) WIN[fr * kTC + 32 * g + lane] = t[g];
+        } else {
+            uint32_t pr[4];
+            int cnt[4];
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) { pr[g] = __ballot_sync(kFull, t[g] != 0u); cnt[g] = __popc(pr[g]); }
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&ctl.alloc, cnt[0] + cnt[1] + cnt[2] + cnt[3]);
+            base = __shfl_sync(kFull, base, 0);
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                if (lane == g) PB[fr * 4 + g] = make_uint2(pr[g], (uint32_t)base);
+                const int idx = base + __popc(pr[g] & lt);
+                if (t[g] != 0u && idx < kSparseWords) WIN[idx] = t[g];
+                base += cnt[g];
+            }
+        }
+    }
+}
+
+}  // namespace
+
+namespace {
+
+enum ItemResult { kItemDone = 0, kItemToGeneral = 1, kItemToDense = 2 };
+
+// One work item = one source of a chain leader, processed by the whole CTA.  All control flow is
+// CTA-uniform.  kItemToGeneral: level 0 cannot answer; kItemToDense (sparse only): the window has
+// more non-zero tile words than the sparse layout holds.
+template <bool SPARSE>
+__device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
+    using C = Cfg<SPARSE>;
     constexpr int NT = kFastThreads;
+    constexpr int HASH = C::kHash;
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
     const uint32_t lt = lanemask_lt();
     const int RW = p.max_px;
     const int NR = (RW + 3) / 4 + 1;
 
-    uint32_t* const OF = smem;
-    uint2* const q0 = (uint2*)(OF + NR * kTC);            // [2][kNW][kSeg] (bits, meta)
-    uint32_t* const hash = (uint32_t*)(q0 + 2 * kFastQCap);
+    // shared memory: window words | (sparse) presence/base table | two frontier buffers | target hash
+    uint32_t* const WIN = smem;
+    uint2* const PB = (uint2*)(WIN + (SPARSE ? kSparseWords : NR * kTC));
+    uint2* const q0 = PB + (SPARSE ? NR * 4 : 0);          // [2][kNW][kSeg] (bits, key)
+    uint32_t* const hash = (uint32_t*)(q0 + 2 * C::kQCap);
     uint32_t* const cand = gscr;
-    uint2* const gq0 = (uint2*)(gscr + kCandCap);         // [2][kNW][kGSeg] global overflow
+    uint2* const gq0 = (uint2*)(gscr + kCandCap);          // [2][kNW][kGSeg] global overflow
     Chain& ch = ctl.ch;
 
     long long tclk = clock64();
@@ -250,22 +335,23 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
     __syncthreads();
     const int nm = ch.nm;
     const int total_t = ch.cum[nm];
-    if (total_t <= 0) return false;
+    if (total_t <= 0) return kItemDone;
 
+    const int sy = p.dets_yx[2 * ((size_t)lead.src_off + si)];
+    const int sx = p.dets_yx[2 * ((size_t)lead.src_off + si) + 1];
     Win w;
-    w.sy = p.dets_yx[2 * ((size_t)lead.src_off + si)];
-    w.sx = p.dets_yx[2 * ((size_t)lead.src_off + si) + 1];
-    w.H = p.H; w.W = p.W; w.Wp = p.Wp; w.RW = RW; w.NR = NR;
-    w.mbits = p.mask_bits + (size_t)lead.mask_idx * p.H * p.Wp;
-    w.oy = w.sy & 3; w.ox = w.sx & 31; w.iw0 = w.sx >> 5;     // only used when the source is in the grid
-    const bool src_in = w.sy >= 0 && w.sy < p.H && w.sx >= 0 && w.sx < p.W;
+    w.tiles = p.mask_tiles + (size_t)lead.mask_idx * p.TH * p.TWp;
+    w.TH = p.TH; w.TWp = p.TWp; w.RW = RW; w.NR = NR;
+    w.oy = sy & 3; w.ox = sx & 31;                         // only used when the source is in the grid
+    w.ty0 = sy >> 2; w.tx0 = (sx >> 5) * 4;
+    const bool src_in = sy >= 0 && sy < p.H && sx >= 0 && sx < p.W;
     const long long r2 = (long long)RW * RW;
-    constexpr int kPassLoad = kHashMaxLoad > NT ? kHashMaxLoad - NT : 0;
+    constexpr int kPassLoad = C::kMaxLoad > NT ? C::kMaxLoad - NT : 0;
 
     int tt = 0;                        // next target of the flattened chain target list
-    for (;;) {                         // passes of <= kHashMaxLoad candidates (one on real data)
-        for (int i = tid; i < kHashSize; i += NT) hash[i] = kEmpty;
-        if (tid == 0) ctl.ncand = 0;
+    for (;;) {                         // passes of <= kMaxLoad candidates (one on real data)
+        for (int i = tid; i < HASH; i += NT) hash[i] = kEmpty;
+        if (tid == 0) { ctl.ncand = 0; ctl.alloc = 0; }
         for (;;) {                     // groups of NT targets
             __syncthreads();
             if (tt >= total_t || ctl.ncand > kPassLoad) break;
@@ -277,7 +363,7 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
                 j = t - ch.cum[m];
                 const int ty = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j)];
                 const int tx = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j) + 1];
-                dy = ty - w.sy; dx = tx - w.sx;
+                dy = ty - sy; dx = tx - sx;
                 const long long d2 = (long long)dy * dy + (long long)dx * dx;
                 if (d2 < r2) {                                        // AxonDetections.py:620-623
                     const bool t_in = ty >= 0 && ty < p.H && tx >= 0 && tx < p.W;
@@ -301,10 +387,10 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
                     const uint32_t slot = (uint32_t)base + __popc(bal & lt);
                     cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
                     int bit;
-                    const uint32_t key = cell_meta(dy, dx, w.oy, w.ox, NR, bit);
+                    const uint32_t key = cell_key(dy, dx, w.oy, w.ox, NR, bit);
                     const uint32_t entry = (key << 16) | ((uint32_t)bit << 11) | slot;
-                    uint32_t h = hash_slot(key);
-                    while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (kHashSize - 1);
+                    uint32_t h = hash_slot<HASH>(key);
+                    while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (HASH - 1);
                 }
             }
             tt += NT;
@@ -312,23 +398,41 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
         const int ncand = ctl.ncand;
         if (ncand > 0) {
             AXB_T(0, tclk);
-            stage_window<NT>(w, OF);
+            stage_window<SPARSE>(w, WIN, PB, ctl);
             __syncthreads();
             AXB_T(1, tclk);
+            if (SPARSE && ctl.alloc > kSparseWords) return kItemToDense;
             if (tid == 0) {            // close the source cell, seed the search with it
                 int bit;
-                const uint32_t key = cell_meta(0, 0, w.oy, w.ox, NR, bit);
-                OF[phys_word(key)] &= ~(1u << bit);
-                q0[0] = make_uint2(1u << bit, key << 2);
+                const uint32_t key = cell_key(0, 0, w.oy, w.ox, NR, bit);
+                int widx = (int)(key & 0x7FFFu);
+                bool there = true;
+                if (SPARSE) {
+                    const uint2 pb = PB[widx >> 5];
+                    there = (pb.x >> (widx & 31)) & 1u;
+                    widx = (int)pb.y + __popc(pb.x & ((1u << (widx & 31)) - 1u));
+                }
+                if (there) WIN[widx] &= ~(1u << bit);
+                q0[0] = make_uint2(1u << bit, key);
                 ctl.wc[0][0] = 1; ctl.wc[0][1] = 0; ctl.wc[0][2] = 0; ctl.wc[0][3] = 0;
             }
             __syncthreads();
 
-            // ---- wavefronts: one thread per frontier entry (tile word, frontier bits) -----------
-            // queue metas are BYTE offsets of the tile word in the window | half << 17 (= key << 2)
-            const uint32_t of_s = smem_u32(OF);
+            // ---- wavefronts: one thread per frontier entry (tile word key, frontier bits) ---------
+            const uint32_t win_s = smem_u32(WIN);
+            const uint32_t pb_s = smem_u32(PB);
             const uint32_t hash_s = smem_u32(hash);
             const uint32_t lastU = (uint32_t)(NR - 1);
+            // shared address of tile word `key` (only when want != 0); want is cleared when the
+            // sparse window holds no such word
+            auto resolve = [&](uint32_t key, uint32_t& want) -> uint32_t {
+                const uint32_t widx = key & 0x7FFFu;
+                if (!SPARSE) return win_s + 4u * widx;
+                const uint2 pb = lds64_if(pb_s + 8u * (widx >> 5), want);
+                const uint32_t bit = 1u << (widx & 31u);
+                if (!(pb.x & bit)) want = 0u;
+                return win_s + 4u * (pb.y + (uint32_t)__popc(pb.x & (bit - 1u)));
+            };
             int unsettled = ncand;     // CTA-uniform: updated from ctl.wc[] after each barrier
             bool hit = false, defer = false;
             for (int j = 0;; ++j) {    // wave j: probe + expand the cells at hop j
@@ -343,8 +447,8 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
 #ifdef AXB_TIMING
                 long long tw = clock64();
 #endif
-                const uint2* const qcur = q0 + (j & 1) * kFastQCap;
-                const uint32_t qnxt_s = smem_u32(q0 + ((j + 1) & 1) * kFastQCap + warp * kSeg);
+                const uint2* const qcur = q0 + (j & 1) * C::kQCap;
+                const uint32_t qnxt_s = smem_u32(q0 + ((j + 1) & 1) * C::kQCap + warp * C::kSeg);
                 const uint2* const gcur = gq0 + (size_t)(j & 1) * kFastGQCap;
                 uint2* const gnxt = gq0 + (size_t)((j + 1) & 1) * kFastGQCap + (size_t)warp * kGSeg;
                 int wn = 0, ws = 0;
@@ -353,28 +457,28 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
                     const int i = base + lane;
                     const int sg = (i >= p1) + (i >= p2) + (i >= p3);
                     const int off = i - (sg == 0 ? 0 : sg == 1 ? p1 : sg == 2 ? p2 : p3);
-                    uint32_t f = 0u, mb = 0u;
+                    uint32_t f = 0u, k0 = 0u;
                     if (i < total) {
-                        const uint2 e = off < kSeg ? qcur[sg * kSeg + off] : gcur[(size_t)sg * kGSeg + (off - kSeg)];
-                        f = e.x; mb = e.y;
+                        const uint2 e = off < C::kSeg ? qcur[sg * C::kSeg + off] : gcur[(size_t)sg * kGSeg + (off - C::kSeg)];
+                        f = e.x; k0 = e.y;
                     }
                     // candidates: cells of the word itself, of the right / left / lower / upper word
-                    const uint32_t cd0 = ((f << 1) & 0xFEFEFEFEu) | ((f >> 1) & 0x7F7F7F7Fu) | (f << 8) | (f >> 8);
-                    const uint32_t cd1 = (f & 0x80808080u) >> 7;
-                    const uint32_t cd2 = (f & 0x01010101u) << 7;
+                    uint32_t cd0 = ((f << 1) & 0xFEFEFEFEu) | ((f >> 1) & 0x7F7F7F7Fu) | (f << 8) | (f >> 8);
+                    uint32_t cd1 = (f & 0x80808080u) >> 7;
+                    uint32_t cd2 = (f & 0x01010101u) << 7;
                     uint32_t cd3 = f >> 24, cd4 = f << 24;
-                    const uint32_t rowm = mb & ~0x1FCu;
-                    const uint32_t m1 = rowm | ((mb + 4u) & 0x1FCu);
-                    const uint32_t m2 = rowm | ((mb - 4u) & 0x1FCu);
-                    uint32_t m3 = mb + 512u, m4 = mb - 512u;
-                    const uint32_t hr = mb >> 9;                      // half << 8 | folded row
-                    if (hr == lastU) m3 = 0x20000u | ((mb + 256u) & 0x1FCu);          // tile row 0 -> 1
-                    if (hr == 256u) m4 = (lastU << 9) | ((mb + 256u) & 0x1FCu);      // tile row 1 -> 0
+                    const uint32_t rowk = k0 & ~127u;
+                    const uint32_t k1 = rowk | ((k0 + 1u) & 127u);
+                    const uint32_t k2 = rowk | ((k0 - 1u) & 127u);
+                    uint32_t k3 = k0 + 128u, k4 = k0 - 128u;
+                    const uint32_t hr = k0 >> 7;                      // half << 8 | folded row
+                    if (hr == lastU) k3 = 0x8000u | ((k0 + 64u) & 127u);              // tile row 0 -> 1
+                    if (hr == 256u) k4 = (lastU << 7) | ((k0 + 64u) & 127u);         // tile row 1 -> 0
                     if (hr == 255u + lastU) cd3 = 0u;                 // window borders (never open anyway)
                     if (hr == 0u) cd4 = 0u;
-                    const uint32_t a0 = of_s + (mb & 0x1FFFFu), a1 = of_s + (m1 & 0x1FFFFu), a2 = of_s + (m2 & 0x1FFFFu);
-                    const uint32_t a3 = of_s + (m3 & 0x1FFFFu), a4 = of_s + (m4 & 0x1FFFFu);
-                    const uint32_t hv = lds_if(hash_s + 4u * hash_slot(mb >> 2), f);
+                    const uint32_t hv = lds_if(hash_s + 4u * hash_slot<HASH>(k0), f);
+                    const uint32_t a0 = resolve(k0, cd0), a1 = resolve(k1, cd1), a2 = resolve(k2, cd2);
+                    const uint32_t a3 = resolve(k3, cd3), a4 = resolve(k4, cd4);
                     const uint32_t o0 = lds_if(a0, cd0) & cd0;
                     const uint32_t o1 = lds_if(a1, cd1) & cd1;
                     const uint32_t o2 = lds_if(a2, cd2) & cd2;
@@ -388,7 +492,7 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
                     // targets among the cells being expanded (hop j, path length j + 1)
                     if (__any_sync(kFull, f != 0u && hv != kEmpty)) {
                         int ns = 0;
-                        if (f != 0u && hv != kEmpty) ns = probe_settle(p, hash, cand, ch, mb >> 2, f, j);
+                        if (f != 0u && hv != kEmpty) ns = probe_settle<HASH>(p, hash, cand, ch, k0, f, j);
                         ws += __reduce_add_sync(kFull, ns);
                     }
                     // append the claims to this warp's segment of the next frontier, lane-major
@@ -398,21 +502,21 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
                     const int tot = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4);
                     if (tot) {
                         int slot = wn + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
-                        if (wn + tot <= kSeg) {
+                        if (wn + tot <= C::kSeg) {
                             uint32_t sa = qnxt_s + 8u * (uint32_t)slot;
-                            sts64_if(sa, c0, mb, c0);   sa += c0 ? 8u : 0u;
-                            sts64_if(sa, c1, m1, c1);   sa += c1 ? 8u : 0u;
-                            sts64_if(sa, c2, m2, c2);   sa += c2 ? 8u : 0u;
-                            sts64_if(sa, c3, m3, c3);   sa += c3 ? 8u : 0u;
-                            sts64_if(sa, c4c, m4, c4c);
-                        } else if (wn + tot <= kSeg + kGSeg) {
+                            sts64_if(sa, c0, k0, c0);   sa += c0 ? 8u : 0u;
+                            sts64_if(sa, c1, k1, c1);   sa += c1 ? 8u : 0u;
+                            sts64_if(sa, c2, k2, c2);   sa += c2 ? 8u : 0u;
+                            sts64_if(sa, c3, k3, c3);   sa += c3 ? 8u : 0u;
+                            sts64_if(sa, c4c, k4, c4c);
+                        } else if (wn + tot <= C::kSeg + kGSeg) {
                             const uint32_t cc[5] = {c0, c1, c2, c3, c4c};
-                            const uint32_t mm[5] = {mb, m1, m2, m3, m4};
+                            const uint32_t kk[5] = {k0, k1, k2, k3, k4};
                             #pragma unroll
                             for (int d = 0; d < 5; ++d) {
                                 if (cc[d]) {
-                                    if (slot < kSeg) sts64_if(qnxt_s + 8u * (uint32_t)slot, cc[d], mm[d], 1u);
-                                    else gnxt[slot - kSeg] = make_uint2(cc[d], mm[d]);
+                                    if (slot < C::kSeg) sts64_if(qnxt_s + 8u * (uint32_t)slot, cc[d], kk[d], 1u);
+                                    else gnxt[slot - C::kSeg] = make_uint2(cc[d], kk[d]);
                                     ++slot;
                                 }
                             }
@@ -430,16 +534,17 @@ __device__ bool run_item_fast(const K2Params& p, const int item, uint32_t* smem,
 #endif
             }
             AXB_T(2, tclk); AXB_C(4, 1);
-            if (defer || (!hit && unsettled > 0)) return true;        // level 0 cannot answer: defer
+            if (defer || (!hit && unsettled > 0)) return kItemToGeneral;   // level 0 cannot answer
         }
         if (tt >= total_t) break;
     }
-    return false;
+    return kItemDone;
 }
 
 }  // namespace
 
-__global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(const K2Params p) {
+// Persistent CTAs over a ticket counter.  The sparse kernel sees every work item first.
+__global__ void __launch_bounds__(kFastThreads, kSparseCtasPerSm) k2_sparse_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
@@ -450,9 +555,40 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
         __syncthreads();
         const int item = ctl.item;
         if (item >= total) break;
-        const bool defer = run_item_fast(p, item, smem, gscr, ctl);
-        if (defer && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+        const int r = run_item_fast<true>(p, item, smem, gscr, ctl);
+        if (threadIdx.x == 0) {
+            if (r == kItemToGeneral) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+            else if (r == kItemToDense) p.dense_list[atomicAdd(&p.counters[3], 1)] = item;
+        }
     }
+}
+
+// Dense windows for the items the sparse layout could not hold.
+__global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(const K2Params p) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ Ctl ctl;
+    uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
+    const int total = p.counters[3];
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[4], 1);
+        __syncthreads();
+        const int t = ctl.item;
+        if (t >= total) break;
+        const int item = p.dense_list[t];
+        const int r = run_item_fast<false>(p, item, smem, gscr, ctl);
+        if (r == kItemToGeneral && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+    }
+}
+
+void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_sparse_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr_set = true;
+    }
+    k2_sparse_kernel<<<grid, kFastThreads, k2_sparse_smem_bytes(p.max_px), stream>>>(p);
 }
 
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {
