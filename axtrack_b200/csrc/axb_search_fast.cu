@@ -402,6 +402,15 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             __syncthreads();
             AXB_T(1, tclk);
             if (SPARSE && ctl.alloc > kSparseWords) return kItemToDense;
+            if (SPARSE) {              // flag the tile-word pairs that hold a target: bits 16.. of PB[].y
+                for (int i = tid; i < HASH; i += NT) {
+                    const uint32_t e = hash[i];
+                    if (e != kEmpty) {
+                        const uint32_t key = e >> 16;
+                        atomicOr(&PB[(key & 0x7FFFu) >> 5].y, 1u << (16u + ((key & 31u) >> 1)));
+                    }
+                }
+            }
             if (tid == 0) {            // close the source cell, seed the search with it
                 int bit;
                 const uint32_t key = cell_key(0, 0, w.oy, w.ox, NR, bit);
@@ -410,7 +419,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 if (SPARSE) {
                     const uint2 pb = PB[widx >> 5];
                     there = (pb.x >> (widx & 31)) & 1u;
-                    widx = (int)pb.y + __popc(pb.x & ((1u << (widx & 31)) - 1u));
+                    widx = (int)(pb.y & 0xFFFFu) + __popc(pb.x & ((1u << (widx & 31)) - 1u));
                 }
                 if (there) WIN[widx] &= ~(1u << bit);
                 q0[0] = make_uint2(1u << bit, key);
@@ -425,13 +434,15 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             const uint32_t lastU = (uint32_t)(NR - 1);
             // shared address of tile word `key` (only when want != 0); want is cleared when the
             // sparse window holds no such word
-            auto resolve = [&](uint32_t key, uint32_t& want) -> uint32_t {
+            // (sparse: PB[].y = index of the group's first word | target flags << 16, returned in aux)
+            auto resolve = [&](uint32_t key, uint32_t& want, uint32_t& aux) -> uint32_t {
                 const uint32_t widx = key & 0x7FFFu;
                 if (!SPARSE) return win_s + 4u * widx;
                 const uint2 pb = lds64_if(pb_s + 8u * (widx >> 5), want);
                 const uint32_t bit = 1u << (widx & 31u);
                 if (!(pb.x & bit)) want = 0u;
-                return win_s + 4u * (pb.y + (uint32_t)__popc(pb.x & (bit - 1u)));
+                aux = pb.y;
+                return win_s + 4u * ((pb.y & 0xFFFFu) + (uint32_t)__popc(pb.x & (bit - 1u)));
             };
             int unsettled = ncand;     // CTA-uniform: updated from ctl.wc[] after each barrier
             bool hit = false, defer = false;
@@ -476,9 +487,13 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     if (hr == 256u) k4 = (lastU << 7) | ((k0 + 64u) & 127u);         // tile row 1 -> 0
                     if (hr == 255u + lastU) cd3 = 0u;                 // window borders (never open anyway)
                     if (hr == 0u) cd4 = 0u;
-                    const uint32_t hv = lds_if(hash_s + 4u * hash_slot<HASH>(k0), f);
-                    const uint32_t a0 = resolve(k0, cd0), a1 = resolve(k1, cd1), a2 = resolve(k2, cd2);
-                    const uint32_t a3 = resolve(k3, cd3), a4 = resolve(k4, cd4);
+                    uint32_t aux0 = 0u, auxn = 0u;
+                    const uint32_t a0 = resolve(k0, cd0, aux0), a1 = resolve(k1, cd1, auxn), a2 = resolve(k2, cd2, auxn);
+                    const uint32_t a3 = resolve(k3, cd3, auxn), a4 = resolve(k4, cd4, auxn);
+                    // may the word hold a target?  sparse: flag of its column pair; dense: its hash slot is in use
+                    bool maybe;
+                    if (SPARSE) maybe = f != 0u && ((aux0 >> (16u + ((k0 & 31u) >> 1))) & 1u);
+                    else maybe = f != 0u && lds_if(hash_s + 4u * hash_slot<HASH>(k0), f) != kEmpty;
                     const uint32_t o0 = lds_if(a0, cd0) & cd0;
                     const uint32_t o1 = lds_if(a1, cd1) & cd1;
                     const uint32_t o2 = lds_if(a2, cd2) & cd2;
@@ -490,9 +505,9 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const uint32_t c3 = claim_if(a3, o3);
                     const uint32_t c4c = claim_if(a4, o4);
                     // targets among the cells being expanded (hop j, path length j + 1)
-                    if (__any_sync(kFull, f != 0u && hv != kEmpty)) {
+                    if (__any_sync(kFull, maybe)) {
                         int ns = 0;
-                        if (f != 0u && hv != kEmpty) ns = probe_settle<HASH>(p, hash, cand, ch, k0, f, j);
+                        if (maybe) ns = probe_settle<HASH>(p, hash, cand, ch, k0, f, j);
                         ws += __reduce_add_sync(kFull, ns);
                     }
                     // append the claims to this warp's segment of the next frontier, lane-major

@@ -319,7 +319,7 @@ def run_b200(args, wl):
             traffic = json.load(open(tf)).get(args.workload)
         except Exception:
             traffic = None
-    roofline = dict(bound='hbm', kernel='k2_search_kernel (one launch = all frame pairs of the block)',
+    roofline = dict(bound='hbm', kernel='K2 launch group = k2_sparse_kernel (dominant, ~90 % by the ncu launch list) + tile/prep/dense/general; one launch = all frame pairs of the block',
                     achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
                     peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
                     algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)),
