@@ -308,3 +308,25 @@ def test_general_path_sources(cuda):
     sub = np.arange(0, len(src), 5)
     a = oracle.cost_matrix_astar(mask, src[sub], dst, 500)
     assert np.array_equal(got[0][sub], a[0]) and np.array_equal(got[1][sub], a[1])
+
+
+@pytest.mark.gpu
+def test_sparse_window_multi_pass_and_dense_fallback(cuda):
+    """(a) a corridor mask whose windows fit the sparse layout with more in-range targets per source
+    than one pass of the sparse kernel's target hash holds (several passes, k2_sparse_kernel);
+    (b) an open field at full radius: the window has more non-zero tile words than the sparse
+    layout holds -> k2_fast_kernel (dense window), diamond-shaped frontiers of ~2000 cells that
+    spill into the global frontier segments."""
+    rng = np.random.default_rng(11)
+    H, W = 1100, 1200
+    mask = synth.make_mask(H, W, seed=5, pitch=(90, 200), width=(6, 16))
+    fg = np.argwhere(mask)
+    src = fg[rng.integers(0, len(fg), 6)].astype(np.int32)
+    dst = fg[rng.integers(0, len(fg), 2500)].astype(np.int32)
+    _check(_gpu_cost(cuda, mask, src, dst, 500), oracle.cost_matrix_rule(mask, src, dst, 500), 'sparse multi-pass')
+    ones = np.ones((H, W), np.uint8)
+    ones[300:800, 600] = 0
+    src = np.array([[550, 560], [10, 10], [1099, 1199], [550, 640]], np.int32)
+    dst = np.stack([rng.integers(0, H, 300), rng.integers(0, W, 300)], 1).astype(np.int32)
+    for max_px in (500, 511, 130):
+        _check(_gpu_cost(cuda, ones, src, dst, max_px), oracle.cost_matrix_rule(ones, src, dst, max_px), ('dense', max_px))
