@@ -24,19 +24,19 @@ MAX_PX = 511
 SYMBOLS = ('axb_create', 'axb_destroy', 'axb_last_error', 'axb_version', 'axb_launch_count',
            'axb_mask_words', 'axb_pack_mask', 'axb_pack_weights', 'axb_cost_matrix_batch',
            'axb_cost_matrix', 'axb_cost_matrix_batch_host', 'axb_cost_matrix_host',
-           'axb_decode_nms', 'axb_decode_nms_host', 'axb_status')
+           'axb_decode_nms', 'axb_decode_nms_host', 'axb_transition_cost_batch', 'axb_status')
 
 
 class PairDesc(ctypes.Structure):
     """struct axb_pair_desc"""
     _fields_ = [('mask_idx', ctypes.c_int32), ('src_off', ctypes.c_int32), ('n_src', ctypes.c_int32),
-                ('dst_off', ctypes.c_int32), ('n_dst', ctypes.c_int32), ('reserved', ctypes.c_int32),
+                ('dst_off', ctypes.c_int32), ('n_dst', ctypes.c_int32), ('time_gap', ctypes.c_int32),
                 ('out_off', ctypes.c_int64)]
 
 
 #: numpy dtype with the same layout as axb_pair_desc
 PAIR_DTYPE = [('mask_idx', '<i4'), ('src_off', '<i4'), ('n_src', '<i4'), ('dst_off', '<i4'),
-              ('n_dst', '<i4'), ('reserved', '<i4'), ('out_off', '<i8')]
+              ('n_dst', '<i4'), ('time_gap', '<i4'), ('out_off', '<i8')]
 
 _lib = None
 
@@ -81,6 +81,8 @@ def load():
     L.axb_decode_nms_host.restype = ci
     L.axb_decode_nms_host.argtypes = [vp, vp, vp, ci, ci, ci, ci, ci, cf, ci, ci,
                                       vp, vp, vp, vp, vp, vp, vp, vp]
+    L.axb_transition_cost_batch.restype = ci
+    L.axb_transition_cost_batch.argtypes = [vp, vp, vp, ci, ci, vp, vp, ci, ci, vp, vp, vp]
     L.axb_status.restype = ci
     L.axb_status.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_int64 * 3)]
     _lib = L

@@ -182,7 +182,7 @@ class B200AssociationMixin:
         offs = np.concatenate([[0], np.cumsum([len(a) for a in yx])]).astype(np.int64)
         masks, of_frame = self._frame_masks()
         keys = [(t, tb) for t in range(T) for tb in range(t - 1, t - (self.MCF_max_num_misses + 2), -1) if tb >= 0]
-        pairs, total, _ = make_pairs([(int(of_frame[t]), int(offs[tb]), len(yx[tb]), int(offs[t]), len(yx[t])) for t, tb in keys])
+        pairs, total, _ = make_pairs([(int(of_frame[t]), int(offs[tb]), len(yx[tb]), int(offs[t]), len(yx[t]), t - tb) for t, tb in keys])
         dev = torch.device('cuda', torch.cuda.current_device())
         bits = ops.pack_mask(torch.from_numpy(masks).to(dev))
         all_yx = np.concatenate(yx) if T else np.zeros((0, 2), np.int32)

@@ -359,6 +359,24 @@ int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_
     return axb_status(c, s, nullptr);
 }
 
+int axb_transition_cost_batch(axb_ctx* c, const int32_t* path_len_dev, const axb_pair_desc* pairs_dev, int n_pairs,
+                              int max_elems_per_pair, const double* cost_tab_dev, const int64_t* arc_tab_dev,
+                              int n_gaps, int max_px, double* cost_dev, int64_t* arc_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_pairs < 0 || n_gaps <= 0 || max_px < 1 || max_px > 65535 || max_elems_per_pair < 0)
+        return bad_arg(c, "axb_transition_cost_batch: bad size");
+    if (n_pairs == 0 || max_elems_per_pair == 0) return AXB_OK;
+    if (!path_len_dev || !pairs_dev || !cost_tab_dev || !cost_dev || (arc_tab_dev && !arc_dev))
+        return bad_arg(c, "axb_transition_cost_batch: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    axb::launch_k3(path_len_dev, pairs_dev, n_pairs, cost_tab_dev, (const long long*)arc_tab_dev, n_gaps, max_px,
+                   cost_dev, arc_tab_dev ? (long long*)arc_dev : nullptr, c->status_dev + 1, max_elems_per_pair,
+                   (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
 int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     if (!c) return AXB_ERR_BAD_ARG;
     AXB_CUDA(c, cudaSetDevice(c->device));
@@ -388,6 +406,7 @@ int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     }
     else if (flags & 2ull) rc = AXB_ERR_UNSUPPORTED_WEIGHT;
     else if (flags & 4ull) rc = AXB_ERR_CAPACITY;
+    else if (flags & 8ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_transition_cost_batch: path length or time gap outside its table"; }
     if (key != ~0ull || flags) {
         c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
         AXB_CUDA(c, cudaMemcpyAsync(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice, s));

@@ -87,6 +87,10 @@ void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_
 void launch_pack_mask_f32(const float* w, int n_masks, int H, int W, uint32_t* bits,
                           unsigned long long* err_flags, cudaStream_t s);
 
+void launch_k3(const int32_t* path_len, const axb_pair_desc* pairs, int n_pairs, const double* cost_tab,
+               const long long* arc_tab, int n_gaps, int max_px, double* cost, long long* arc,
+               unsigned long long* err_flags, int max_elems_per_pair, cudaStream_t stream);
+
 // ---- K1 ------------------------------------------------------------------------------------
 struct K1Params {
     const float* Y;              // [F][ntiles][Sx][Sy][3]

@@ -177,7 +177,7 @@ namespace {
 
 constexpr int kNW = kFastThreads / 32;            // warps per search
 constexpr int kGSeg = kFastGQCap / kNW;           // global overflow entries per warp per buffer
-static_assert(kNW == 4, "Ctl::wc holds one word per warp in one 16-byte row");
+static_assert(kNW >= 1 && kNW <= 4, "Ctl::wc holds one word per warp in one 16-byte row");
 
 template <bool SPARSE> struct Cfg;
 template <> struct Cfg<false> {
@@ -424,6 +424,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 if (there) WIN[widx] &= ~(1u << bit);
                 q0[0] = make_uint2(1u << bit, key);
                 ctl.wc[0][0] = 1; ctl.wc[0][1] = 0; ctl.wc[0][2] = 0; ctl.wc[0][3] = 0;
+                ctl.wc[1][0] = 0; ctl.wc[1][1] = 0; ctl.wc[1][2] = 0; ctl.wc[1][3] = 0;   // words of absent warps stay 0
             }
             __syncthreads();
 

@@ -84,7 +84,7 @@ class HostAssociator:
                 if T else np.zeros((0, 2), np.int32))
         keys = frame_pair_keys(T, max_num_misses)
         pairs, total, _ = make_pairs([(0 if mask_of_frame is None else int(mask_of_frame[t]), int(offs[tb]),
-                                       len(frame_dets_yx[tb]), int(offs[t]), len(frame_dets_yx[t])) for t, tb in keys])
+                                       len(frame_dets_yx[tb]), int(offs[t]), len(frame_dets_yx[t]), t - tb) for t, tb in keys])
         pl, un, wc = self.cost_matrices_flat(masks, dets, pairs, total, max_px, want_cost)
         res = {}
         for k, pd in zip(keys, pairs):

@@ -187,3 +187,36 @@ def raise_status(pairs=None, dets_yx_host=None, device=None):
     if rc == _lib.ERR_OOB_GOAL:
         raise ValueError('Goal lies outside grid.')
     raise _lib.AxbError(rc, 'device-side status')
+
+
+def transition_cost_batch(path_len, pairs, cost_tab, arc_tab=None, pairs_dev=None):
+    """Transition costs of all frame pairs in one launch (K3).
+
+    path_len int32 CUDA flat (output of ``cost_matrix_batch`` for the same ``pairs``); pairs numpy
+    struct array with ``time_gap`` filled; cost_tab float64 [n_gaps, max_px+1] / arc_tab int64 (host
+    numpy or CUDA) from ``mincostflow_models.transition_tables``.  -> (cost float64 CUDA flat,
+    arc int64 CUDA flat | None).  Replaces mincostflow_models.py:100-119 and
+    offline_mincostflow.py:192-198 (vis_sim_weight = 0)."""
+    path_len = _need_cuda(path_len, 'path_len', torch.int32)
+    dev = path_len.device
+    ctx = get_context(dev)
+    cost_tab = torch.as_tensor(np.ascontiguousarray(cost_tab) if isinstance(cost_tab, np.ndarray) else cost_tab,
+                               dtype=torch.float64).to(dev).contiguous()
+    n_gaps, n_d = cost_tab.shape
+    if arc_tab is not None:
+        arc_tab = torch.as_tensor(np.ascontiguousarray(arc_tab) if isinstance(arc_tab, np.ndarray) else arc_tab,
+                                  dtype=torch.int64).to(dev).contiguous()
+        assert arc_tab.shape == cost_tab.shape
+    n_pairs = len(pairs)
+    total = int(path_len.numel())
+    cost = torch.empty(total, dtype=torch.float64, device=dev)
+    arc = torch.empty(total, dtype=torch.int64, device=dev) if arc_tab is not None else None
+    if n_pairs and total:
+        if pairs_dev is None:
+            pairs_dev = torch.from_numpy(pairs.view(np.uint8).reshape(-1).copy()).to(dev)
+        max_elems = int((pairs['n_src'].astype(np.int64) * pairs['n_dst']).max())
+        ctx.check(ctx.lib.axb_transition_cost_batch(
+            ctx.handle, path_len.data_ptr(), pairs_dev.data_ptr(), n_pairs, max_elems,
+            cost_tab.data_ptr(), arc_tab.data_ptr() if arc_tab is not None else None, int(n_gaps), int(n_d - 1),
+            cost.data_ptr(), arc.data_ptr() if arc is not None else None, _stream()))
+    return cost, arc

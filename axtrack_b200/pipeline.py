@@ -28,7 +28,7 @@ def build_pairs(n_out, cap, keys, mask_of_frame=None):
     entries = []
     for t, tb in keys:
         m = 0 if mask_of_frame is None else int(mask_of_frame[t])
-        entries.append((m, tb * cap, int(n_out[tb]), t * cap, int(n_out[t])))
+        entries.append((m, tb * cap, int(n_out[tb]), t * cap, int(n_out[t]), t - tb))
     return ops.make_pairs(entries)
 
 
@@ -52,6 +52,13 @@ class Association:
         yx = self.det['yx'][t, :n].cpu().numpy()
         return dict(conf=self.det['conf'][t, :n].cpu().numpy(), x=yx[:, 1].astype(np.int64),
                     y=yx[:, 0].astype(np.int64), keep_idx=self.det['keep_idx'][t, :n].cpu().numpy().astype(np.int64))
+
+    def transition_costs(self, max_px=500, miss_rate=0.6, max_num_misses=1, cost_threshold=None):
+        """K3: (cost float64 CUDA flat, arc int64 CUDA flat | None) for every pair, laid out like
+        ``path_len`` (mincostflow_models.py:100-119, offline_mincostflow.py:192-198; weight 0)."""
+        from .mincostflow_models import transition_tables
+        ct, at = transition_tables(max_px, miss_rate, max_num_misses, 0.0, cost_threshold)
+        return ops.transition_cost_batch(self.path_len, self.pairs, ct, at)
 
     def pair_matrices(self):
         """{(t, t_bef): (path_len [n_pred,n_cur] int32, unreachable uint8, wcost float32|None)} on the host."""

@@ -306,6 +306,15 @@ def run_b200(args, wl):
         torch.cuda.synchronize()
         if i >= 3:
             k1ms.append(e0.elapsed_time(e1))
+    k3ms = []          # K3 (transition costs + arc costs of every pair), reported beside the metric, not inside it
+    for i in range(3 + args.steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res.transition_costs(MAX_PX, 0.6, MAX_MISSES, cost_threshold=0.7)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            k3ms.append(e0.elapsed_time(e1))
     yx_h = det['yx'].cpu().numpy()
     frame_dets = [yx_h[t, :int(n_out[t])] for t in range(len(n_out))]
     alg = algorithmic_bytes(frame_dets, res.keys, H, W, MAX_PX)
@@ -322,7 +331,7 @@ def run_b200(args, wl):
     roofline = dict(bound='hbm', kernel='K2 launch group = k2_sparse_kernel (dominant, ~90 % by the ncu launch list) + tile/prep/dense/general; one launch = all frame pairs of the block',
                     achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
                     peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
-                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)),
+                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)),
                     traffic=traffic)
 
     # ---- e2e: host buffers through the C ABI ------------------------------------------------------

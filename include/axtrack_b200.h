@@ -50,7 +50,7 @@ typedef struct axb_pair_desc {
     int32_t n_src;      /* n_pred                                                              */
     int32_t dst_off;    /* first target detection in dets_yx_dev                              */
     int32_t n_dst;      /* n_cur                                                               */
-    int32_t reserved;
+    int32_t time_gap;   /* t - t_bef; read by axb_transition_cost_batch only (0 = not given)      */
     int64_t out_off;    /* element offset of this pair's [n_src, n_dst] block in the outputs  */
 } axb_pair_desc;
 
@@ -161,6 +161,24 @@ int axb_decode_nms_host(axb_ctx* ctx, const float* Y_host, const int32_t* tile_y
                         int cap,
                         float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_cell_host, int32_t* n_pre_host,
                         float* conf_host, int32_t* yx_host, int32_t* keep_idx_host, int32_t* n_out_host);
+
+/* ---- transition costs ------------------------------------------------------------------
+ * Replaces the arithmetic of mincostflow_models.transition_model (mincostflow_models.py:100-119)
+ * and the arc cost int(multi_factor * cost) of libmot's graph builder
+ * (libmot/libmot/data_association/offline_mincostflow.py:192-198) for vis_sim_weight = 0.
+ * cost_tab_dev  float64 [n_gaps][max_px + 1]: cost of path length d at time gap g + 1, evaluated
+ *               by the caller with the reference's own numpy expression (so every value is
+ *               bit-identical by construction; axtrack_b200/mincostflow_models.py does it)
+ * arc_tab_dev   int64 [n_gaps][max_px + 1] or NULL: int(1e5 * cost), or the caller's "no arc"
+ *               sentinel where cost > cost_threshold (offline_mincostflow.py:194)
+ * pairs_dev[i].time_gap selects the table row; path_len_dev is the output of
+ * axb_cost_matrix_batch with the same pair descriptors.  cost_dev float64 / arc_dev int64 (NULL
+ * when arc_tab_dev is NULL) use the same [n_src, n_dst] blocks at out_off.  A path length
+ * outside [0, max_px] or a time gap outside [1, n_gaps] sets AXB_ERR_BAD_ARG in axb_status. */
+int axb_transition_cost_batch(axb_ctx* ctx, const int32_t* path_len_dev,
+                              const axb_pair_desc* pairs_dev, int n_pairs, int max_elems_per_pair,
+                              const double* cost_tab_dev, const int64_t* arc_tab_dev, int n_gaps, int max_px,
+                              double* cost_dev, int64_t* arc_dev, void* stream);
 
 /* ---- status ----------------------------------------------------------------------------
  * Synchronises `stream` and returns the sticky device-side status of the calls issued on this
