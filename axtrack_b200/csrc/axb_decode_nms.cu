@@ -248,7 +248,10 @@ size_t k1_scratch_per_frame(int ncell, int npad) {
 }
 
 void launch_k1(const K1Params& p, cudaStream_t stream) {
-    k1_decode_nms_kernel<kK1Threads><<<p.F, kK1Threads, 0, stream>>>(p);
+    // one CTA per frame; frames with many grid cells (configs[4]: 36864) get 32 warps for the
+    // decode pass, the bitonic sort and the NMS rounds
+    if ((long long)p.ntiles * p.Sx * p.Sy > 4096) k1_decode_nms_kernel<1024><<<p.F, 1024, 0, stream>>>(p);
+    else k1_decode_nms_kernel<kK1Threads><<<p.F, kK1Threads, 0, stream>>>(p);
 }
 
 // ---------------------------------------------------------------------------------------------

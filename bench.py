@@ -392,16 +392,72 @@ def run_b200(args, wl):
         dist.destroy_process_group()
 
 
+def run_c5(args):
+    """BASELINE configs[4] / SURVEY 8(d) C5: detector-output stress, 8192x8192 frames (256 tiles of
+    12x12 cells) through the fused decode+threshold+stitch+NMS kernel K1; sweep of frames per launch
+    and of candidate density.  One JSON line; value = frames/s at 64 frames per launch, ~3000
+    detections per frame.  Not the headline metric (that is frame-pairs/s on configs[1])."""
+    import torch
+    from axtrack_b200 import ops, synth
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: axtrack_b200 has no CPU fallback')
+    import oracle
+    dev = torch.device('cuda', 0)
+    H = W = 8192
+    tt = synth.tile_table(H, W)
+    td = torch.from_numpy(tt).to(dev)
+    rng = np.random.default_rng(0)
+    sweep = []
+    peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    headline = None
+    for n_det in (800, 3000, 12000):
+        dets = np.stack([rng.integers(0, H, n_det), rng.integers(0, W, n_det)], 1)
+        Y1 = synth.make_head_tensor(dets, H, W, seed=n_det)[0]
+        want = oracle.decode_stitch_nms(Y1, tt)                       # checker: the timed kernel's result is right
+        for F in (1, 8, 64, 512):
+            Yd = torch.from_numpy(Y1).to(dev).unsqueeze(0).repeat(F, 1, 1, 1, 1).contiguous()
+            ms = []
+            for i in range(3 + args.steps):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                o = ops.decode_nms(Yd, td, want_pre=False)
+                e1.record()
+                torch.cuda.synchronize()
+                if i >= 3:
+                    ms.append(e0.elapsed_time(e1))
+            n_out = int(o['n_out'][F - 1])
+            assert n_out == len(want['keep_idx']) and np.array_equal(o['keep_idx'][F - 1, :n_out].cpu().numpy(), want['keep_idx'])
+            t = float(np.mean(ms)) * 1e-3
+            alg = F * (Y1.nbytes + n_out * 16)
+            row = dict(dets_per_frame=n_out, frames_per_launch=F, ms=t * 1e3, frames_per_s=F / t, gbs=alg / t / 1e9, frac=alg / t / 1e9 / peak)
+            sweep.append(row)
+            if n_det == 3000 and F == 64:
+                headline = row
+            del Yd
+    line = dict(metric='frames/sec (fused decode+threshold+stitch+NMS, K1)', value=headline['frames_per_s'], unit='frames/s',
+                n_gpus=1, steps=args.steps, warmup=3, ms_per_step=headline['ms'], higher_is_better=True, scaling='weak',
+                vs_baseline=None, dtype='f32', data='synthetic',
+                config=dict(workload='configs[4]: detector-output stress, 8192x8192 frames tiled through the YOLO_AXTrack head (256 tiles x 12x12 cells), fused decode+NMS sweep',
+                            frames_per_launch=64, dets_per_frame=headline['dets_per_frame'], l2='inputs are re-read from HBM/L2 each launch; 64 frames = 28 MB'),
+                roofline=dict(bound='hbm', kernel='k1_decode_nms_kernel', achieved=headline['gbs'], peak=peak, unit='GB/s', frac=headline['frac'],
+                              note='one CTA per frame: latency bound below ~148 frames per launch'),
+                sweep=sweep)
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
+    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c5'])
     ap.add_argument('--cpu-calls', type=int, default=1200, help='in-range A* calls of the cpu_baseline sample (~15 ms each at 2048^2)')
     ap.add_argument('--ref-calls', type=int, default=250, help='in-range A* calls per --impl reference step')
     args = ap.parse_args()
+    if args.workload == 'c5':
+        return run_c5(args)
     wl = WORKLOADS[args.workload]
     if args.impl == 'reference':
         run_reference(args, wl)

@@ -330,3 +330,28 @@ def test_sparse_window_multi_pass_and_dense_fallback(cuda):
     dst = np.stack([rng.integers(0, H, 300), rng.integers(0, W, 300)], 1).astype(np.int32)
     for max_px in (500, 511, 130):
         _check(_gpu_cost(cuda, ones, src, dst, max_px), oracle.cost_matrix_rule(ones, src, dst, max_px), ('dense', max_px))
+
+
+@pytest.mark.gpu
+def test_decode_nms_8192_frames(cuda):
+    """BASELINE configs[4] shape: 8192x8192 frames = 256 tiles x 12x12 cells, thousands of candidates
+    per frame (the sort leaves shared memory), several frames per launch; survivor indices,
+    coordinates and confidences bit-exact vs the numpy port of the reference's pandas code."""
+    from axtrack_b200 import ops
+    H = W = 8192
+    tt = synth.tile_table(H, W)
+    rng = np.random.default_rng(3)
+    Ys, wants = [], []
+    for n_det in (50, 2500, 9000):
+        dets = np.stack([rng.integers(0, H, n_det), rng.integers(0, W, n_det)], 1)
+        Y = synth.make_head_tensor(dets, H, W, seed=n_det)[0]
+        Ys.append(Y); wants.append(oracle.decode_stitch_nms(Y, tt))
+    o = ops.decode_nms(cuda.from_numpy(np.stack(Ys)).cuda(), cuda.from_numpy(tt).cuda())
+    ops.raise_status()
+    for f, w in enumerate(wants):
+        n = int(o['n_out'][f])
+        assert n == len(w['keep_idx']) and int(o['n_pre'][f]) == len(w['pre_conf'])
+        assert np.array_equal(o['keep_idx'][f, :n].cpu().numpy(), w['keep_idx'])
+        yx = o['yx'][f, :n].cpu().numpy()
+        assert np.array_equal(yx[:, 0], w['y']) and np.array_equal(yx[:, 1], w['x'])
+        assert np.array_equal(o['conf'][f, :n].cpu().numpy(), w['conf'])
