@@ -109,14 +109,17 @@ __device__ __forceinline__ uint32_t window_tile(const Win& w, int tr, int tc, in
     return __ldg(w.tiles + (size_t)ty * w.TWp + tx) & m;
 }
 
-// tile word of folded row fr, folded column col: the upper-half and the lower-half candidates
+// tile word of folded row fr, folded column col.  A folded column holds tile column col-64 or
+// col+64 of the upper tile row and tile column col or col-128 of the lower one; at most one of
+// each pair lies inside the row's span, and the spans of the two halves never overlap.
 __device__ __forceinline__ uint32_t folded_tile(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l) {
-    const int tr_u = fr - w.NR + 1;
-    uint32_t t = window_tile(w, tr_u, col - 64, hwi_u, hwo_u);
-    if (col < 8) t |= window_tile(w, tr_u, col + 64, hwi_u, hwo_u);
+    int tc = col - 64;
+    if (8 * tc - w.ox + 7 < -hwo_u) tc += 128;
+    uint32_t t = window_tile(w, fr - w.NR + 1, tc, hwi_u, hwo_u);
     if (fr + 1 <= w.NR - 1) {
-        if (col < 72) t |= window_tile(w, fr + 1, col, hwi_l, hwo_l);
-        if (col >= 56) t |= window_tile(w, fr + 1, col - 128, hwi_l, hwo_l);
+        tc = col;
+        if (8 * tc - w.ox > hwo_l) tc -= 128;
+        t |= window_tile(w, fr + 1, tc, hwi_l, hwo_l);
     }
     return t;
 }
@@ -432,6 +435,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             const uint32_t win_s = smem_u32(WIN);
             const uint32_t pb_s = smem_u32(PB);
             const uint32_t hash_s = smem_u32(hash);
+            const uint32_t q_s = smem_u32(q0);
             const uint32_t lastU = (uint32_t)(NR - 1);
             // shared address of tile word `key` (only when want != 0); want is cleared when the
             // sparse window holds no such word
@@ -459,21 +463,21 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
 #ifdef AXB_TIMING
                 long long tw = clock64();
 #endif
-                const uint2* const qcur = q0 + (j & 1) * C::kQCap;
-                const uint32_t qnxt_s = smem_u32(q0 + ((j + 1) & 1) * C::kQCap + warp * C::kSeg);
-                const uint2* const gcur = gq0 + (size_t)(j & 1) * kFastGQCap;
-                uint2* const gnxt = gq0 + (size_t)((j + 1) & 1) * kFastGQCap + (size_t)warp * kGSeg;
+                const uint32_t qcur_s = q_s + (uint32_t)(j & 1) * (C::kQCap * 8u);
+                const uint32_t qnxt_s = q_s + (uint32_t)((j + 1) & 1) * (C::kQCap * 8u) + (uint32_t)warp * (C::kSeg * 8u);
                 int wn = 0, ws = 0;
                 bool wovf = false;
                 for (int base = warp * 32; base < total; base += NT) {
                     const int i = base + lane;
                     const int sg = (i >= p1) + (i >= p2) + (i >= p3);
                     const int off = i - (sg == 0 ? 0 : sg == 1 ? p1 : sg == 2 ? p2 : p3);
-                    uint32_t f = 0u, k0 = 0u;
-                    if (i < total) {
-                        const uint2 e = off < C::kSeg ? qcur[sg * C::kSeg + off] : gcur[(size_t)sg * kGSeg + (off - C::kSeg)];
-                        f = e.x; k0 = e.y;
+                    const bool act = i < total;
+                    uint2 e = lds64_if(qcur_s + 8u * (uint32_t)(sg * C::kSeg + off), act && off < C::kSeg);
+                    if (__any_sync(kFull, act && off >= C::kSeg)) {           // entries that spilled to global memory
+                        if (act && off >= C::kSeg)
+                            e = (gq0 + (size_t)(j & 1) * kFastGQCap)[(size_t)sg * kGSeg + (off - C::kSeg)];
                     }
+                    const uint32_t f = e.x, k0 = e.y;
                     // candidates: cells of the word itself, of the right / left / lower / upper word
                     uint32_t cd0 = ((f << 1) & 0xFEFEFEFEu) | ((f >> 1) & 0x7F7F7F7Fu) | (f << 8) | (f >> 8);
                     uint32_t cd1 = (f & 0x80808080u) >> 7;
@@ -528,6 +532,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                         } else if (wn + tot <= C::kSeg + kGSeg) {
                             const uint32_t cc[5] = {c0, c1, c2, c3, c4c};
                             const uint32_t kk[5] = {k0, k1, k2, k3, k4};
+                            uint2* const gnxt = gq0 + (size_t)((j + 1) & 1) * kFastGQCap + (size_t)warp * kGSeg;
                             #pragma unroll
                             for (int d = 0; d < 5; ++d) {
                                 if (cc[d]) {

@@ -34,6 +34,8 @@ WORKLOADS = {
     'c2': dict(H=2048, W=2048, T=100, n_dets=250, desc='configs[1]: synthetic 2048x2048 timelapse, 100 frames, ~200 dets/frame, deployed params.pkl tiling (512 px tiles, 12x12 cells)'),
     # configs[2]: dense 4096x4096, 200 frames, ~800 dets/frame
     'c3': dict(H=4096, W=4096, T=200, n_dets=1000, desc='configs[2]: dense synthetic 4096x4096 timelapse, 200 frames, ~800 dets/frame'),
+    # configs[3]: long 2048x2048 timelapse, 2000 frames (per rank under torchrun: weak scaling)
+    'c4': dict(H=2048, W=2048, T=2000, n_dets=250, desc='configs[3]: long synthetic 2048x2048 timelapse, 2000 frames, ~200 dets/frame, sharded by timepoint'),
     # configs[0] shape (examples/test.py), 2 frames
     'c1': dict(H=1969, W=3868, T=2, n_dets=250, desc='configs[0]: example timelapse shape 1969x3868, 2 frames'),
 }
