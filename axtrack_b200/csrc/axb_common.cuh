@@ -77,6 +77,18 @@ inline size_t k2_gen_smem_bytes(int max_px) {
 constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
 
+// Function attributes are per device: true the first time the calling thread's current device is
+// seen for `flags` (one 64-bit word per kernel), so that the opt-in shared-memory size is set once
+// on every device a process uses.
+inline bool first_use_on_device(unsigned long long& flags) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (flags & bit) return false;
+    flags |= bit;
+    return true;
+}
+
 void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
                     int* next_same, int* counters, cudaStream_t stream);
 void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);

@@ -501,10 +501,9 @@ void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, i
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0ull;
+    if (first_use_on_device(attr_set)) {
         cudaFuncSetAttribute(k2_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_gen_smem_bytes(AXB_MAX_PX));
-        attr_set = true;
     }
     k2_general_kernel<<<grid, kK2Threads, k2_gen_smem_bytes(p.max_px), stream>>>(p);
 }

@@ -603,21 +603,19 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
 }
 
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0ull;
+    if (first_use_on_device(attr_set)) {
         cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_sparse_smem_bytes(AXB_MAX_PX));
         cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        attr_set = true;
     }
     k2_sparse_kernel<<<grid, kFastThreads, k2_sparse_smem_bytes(p.max_px), stream>>>(p);
 }
 
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_set = 0ull;
+    if (first_use_on_device(attr_set)) {
         cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_fast_smem_bytes(AXB_MAX_PX));
         cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        attr_set = true;
     }
     k2_fast_kernel<<<grid, kFastThreads, k2_fast_smem_bytes(p.max_px), stream>>>(p);
 }
