@@ -25,6 +25,8 @@ struct axb_ctx {
     int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;   // [work | all | next] x prefix_cap
     int* gen_list = nullptr;          size_t gen_list_bytes = 0;
     int* dense_list = nullptr;        size_t dense_list_bytes = 0;
+    uint8_t* trace_par = nullptr;                                      // K4: per general CTA entry directions
+    int* trace_iota = nullptr;        size_t trace_iota_bytes = 0;
     uint32_t* k2_tiles = nullptr;     size_t k2_tiles_bytes = 0;       // 8x4-pixel tile words of the masks of the current call
     // K1
     uint8_t* k1_scratch = nullptr;    size_t k1_scratch_bytes = 0;
@@ -118,6 +120,7 @@ void axb_destroy(axb_ctx* c) {
     cudaDeviceSynchronize();
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
+    cudaFree(c->trace_par); cudaFree(c->trace_iota);
     cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
     cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1);
@@ -182,6 +185,7 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     p.max_px = max_px; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
+    p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
     axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
     axb::launch_k2_fast(p, std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src)), s);
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
@@ -357,6 +361,62 @@ int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_
     if (pre_yx_host) AXB_CUDA(c, cudaMemcpyAsync(pre_yx_host, d_pyx, 2 * nFC, cudaMemcpyDeviceToHost, s));
     if (pre_cell_host) AXB_CUDA(c, cudaMemcpyAsync(pre_cell_host, d_ptile, nFC, cudaMemcpyDeviceToHost, s));
     return axb_status(c, s, nullptr);
+}
+
+int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
+                    const int32_t* req_host, int n_req, int max_px,
+                    int32_t* path_yx_dev, int32_t* path_len_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_req < 0 || H <= 0 || W <= 0 || n_masks <= 0) return bad_arg(c, "axb_trace_paths: bad size");
+    if (max_px < 1 || max_px > AXB_MAX_PX) return bad_arg(c, "axb_trace_paths: max_px outside [1, AXB_MAX_PX]");
+    if (n_req == 0) return AXB_OK;
+    if (!mask_bits_dev || !req_host || !path_yx_dev || !path_len_dev) return bad_arg(c, "axb_trace_paths: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = ensure_k2(c, n_req, n_req);
+    if (rc != AXB_OK) return rc;
+    if (!c->trace_par) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par, (size_t)c->k2_gen_ctas * axb::kTraceParBytes));
+    // one 1 x 1 frame pair per request: detections rows 2i (source), 2i+1 (target)
+    std::vector<int32_t> dets((size_t)n_req * 4);
+    std::vector<axb_pair_desc> pairs((size_t)n_req);
+    std::vector<int> iota((size_t)n_req + 1);
+    for (int i = 0; i < n_req; ++i) {
+        const int32_t* r = req_host + 5 * (size_t)i;
+        if (r[0] < 0 || r[0] >= n_masks) return bad_arg(c, "axb_trace_paths: mask index out of range");
+        dets[4 * (size_t)i] = r[1]; dets[4 * (size_t)i + 1] = r[2]; dets[4 * (size_t)i + 2] = r[3]; dets[4 * (size_t)i + 3] = r[4];
+        axb_pair_desc& pd = pairs[i];
+        memset(&pd, 0, sizeof pd);
+        pd.mask_idx = r[0]; pd.src_off = 2 * i; pd.n_src = 1; pd.dst_off = 2 * i + 1; pd.n_dst = 1; pd.out_off = i;
+        iota[i] = i;
+    }
+    iota[n_req] = n_req;
+    if ((rc = grow(c, &c->st_dets, &c->st_dets_bytes, dets.size() * 4)) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_pairs, &c->st_pairs_bytes, pairs.size() * sizeof(axb_pair_desc))) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_plen, &c->st_plen_bytes, (size_t)n_req * 4)) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->st_unr, &c->st_unr_bytes, (size_t)n_req)) != AXB_OK) return rc;
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_dets, dets.data(), dets.size() * 4, cudaMemcpyHostToDevice, s));      // pageable: staged before return
+    AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, pairs.data(), pairs.size() * sizeof(axb_pair_desc), cudaMemcpyHostToDevice, s));
+    int* const work_prefix = c->prefix_dev;
+    int* const all_prefix = c->prefix_dev + c->prefix_cap;
+    int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
+    axb::launch_k2_prep(c->st_pairs, n_req, work_prefix, all_prefix, next_same, c->counters, s);
+    c->last_n_pairs = n_req;
+    // every request goes straight to the all-levels kernel: gen_list = 0 .. n-1, counters[1] = n
+    AXB_CUDA(c, cudaMemcpyAsync(c->gen_list, iota.data(), (size_t)n_req * sizeof(int), cudaMemcpyHostToDevice, s));
+    AXB_CUDA(c, cudaMemcpyAsync(c->counters + 1, &iota[n_req], sizeof(int), cudaMemcpyHostToDevice, s));
+    axb::K2Params p;
+    memset(&p, 0, sizeof p);
+    p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = (W + 31) / 32;
+    p.dets_yx = c->st_dets; p.pairs = c->st_pairs; p.n_pairs = n_req;
+    p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
+    p.max_px = max_px; p.path_len = c->st_plen; p.unreachable = c->st_unr; p.wcost = nullptr;
+    p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
+    p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
+    p.trace_par = c->trace_par; p.trace_yx = path_yx_dev; p.trace_len = path_len_dev;
+    axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, n_req)), s);
+    c->launches += 2;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
 }
 
 int axb_transition_cost_batch(axb_ctx* c, const int32_t* path_len_dev, const axb_pair_desc* pairs_dev, int n_pairs,

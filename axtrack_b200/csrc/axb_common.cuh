@@ -61,6 +61,10 @@ struct K2Params {
     int* counters;               // [0] sparse ticket, [1] general list length, [2] general ticket, [3] dense list length, [4] dense ticket
     int* gen_list;               // work items deferred to the general kernel
     int* dense_list;             // work items whose window does not fit the sparse layout
+    // path tracing (k2_general_kernel only; NULL otherwise): one (source, target) request per pair
+    uint8_t* trace_par;          // per general CTA kTraceParBytes: direction a window cell was entered from
+    int32_t* trace_yx;           // [n_pairs][max_px][2] (row, col), start -> goal
+    int32_t* trace_len;          // [n_pairs] pixels on the path, 0 = None
     unsigned long long* err_key; // atomicMin: (item in reference order << 26 | target << 2 | code)
 };
 
@@ -75,6 +79,7 @@ inline size_t k2_gen_smem_bytes(int max_px) {
     return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
 }
 constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap;
+constexpr size_t kTraceParBytes = (size_t)(AXB_MAX_PX + 1) * kRowBits;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
 
 // Function attributes are per device: true the first time the calling thread's current device is

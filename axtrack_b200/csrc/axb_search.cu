@@ -233,6 +233,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
     const bool src_in = s.sy >= 0 && s.sy < p.H && s.sx >= 0 && s.sx < p.W;
     const long long r2 = (long long)RW * RW;
     const int o = s.o;
+    uint8_t* const par = p.trace_par ? p.trace_par + (size_t)blockIdx.x * kTraceParBytes : nullptr;
 
     int tt = 0;                        // next target of the flattened chain target list
     for (;;) {                         // passes of <= kHashMaxLoad candidates (one on real data)
@@ -358,6 +359,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                                 const uint32_t bit = 1u << (idx & 31);
                                 if (OF[pw] & bit) got_fg = (atomicAnd(&OF[pw], ~bit) & bit) != 0;
                                 else if (OB[pw] & bit) got_bg = (atomicAnd(&OB[pw], ~bit) & bit) != 0;
+                                if (par && (got_fg || got_bg)) par[idx] = (uint8_t)dir;   // entered from (dy, cx)
                             }
                             const uint32_t bf = __ballot_sync(kFull, got_fg);
                             const uint32_t bb = __ballot_sync(kFull, got_bg);
@@ -421,7 +423,32 @@ __global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Param
         __syncthreads();
         const int t = ctl.item;
         if (t >= total) break;
-        run_item<true, kK2Threads>(p, p.gen_list[t], smem, gscr, ctl);
+        const int item = p.gen_list[t];
+        run_item<true, kK2Threads>(p, item, smem, gscr, ctl);
+        if (p.trace_par) {             // one (source, target) request per pair: walk the entry directions back
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const axb_pair_desc pd = p.pairs[item];
+                const int sy = p.dets_yx[2 * (size_t)pd.src_off], sx = p.dets_yx[2 * (size_t)pd.src_off + 1];
+                const int ty = p.dets_yx[2 * (size_t)pd.dst_off], tx = p.dets_yx[2 * (size_t)pd.dst_off + 1];
+                const uint8_t* const par = p.trace_par + (size_t)blockIdx.x * kTraceParBytes;
+                int32_t* const out = p.trace_yx + (size_t)item * p.max_px * 2;
+                int L = p.unreachable[pd.out_off] ? 0 : p.path_len[pd.out_off];
+                const int x0 = sx & ~31, o = sx & 31;
+                int dy = ty - sy, cx = tx - x0;
+                for (int n = L - 1; n >= 1; --n) {
+                    out[2 * n] = sy + dy; out[2 * n + 1] = x0 + cx;
+                    const int d = par[fold_index(dy, cx, p.max_px)] & 3;
+                    dy -= d == 0 ? -1 : d == 3 ? 1 : 0;
+                    cx -= d == 1 ? -1 : d == 2 ? 1 : 0;
+                }
+                if (L >= 1) {
+                    out[0] = sy + dy; out[1] = x0 + cx;
+                    if (dy != 0 || cx != o) L = -1;      // cannot happen: the walk must end at the source
+                }
+                p.trace_len[item] = L;
+            }
+        }
     }
 }
 // Chains + prefix sums + counter reset, one CTA.

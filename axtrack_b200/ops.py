@@ -220,3 +220,26 @@ def transition_cost_batch(path_len, pairs, cost_tab, arc_tab=None, pairs_dev=Non
             cost_tab.data_ptr(), arc_tab.data_ptr() if arc_tab is not None else None, int(n_gaps), int(n_d - 1),
             cost.data_ptr(), arc.data_ptr() if arc is not None else None, _stream()))
     return cost, arc
+
+
+def trace_paths(mask_bits, W, requests, max_px=500):
+    """Path PIXELS of selected (source, target) pairs (K4).
+
+    mask_bits int32 CUDA [n_masks, H, Wp]; requests int32 [n, 5] rows (mask_idx, sy, sx, ty, tx)
+    (numpy).  -> (yx int32 CUDA [n, max_px, 2] (row, col) start -> goal, length int32 CUDA [n]; 0 = the
+    reference's None).  Replaces utils._compute_astar_path -> pyastar2d.astar_path
+    (utils.py:351-390) for the pairs whose pixels are wanted."""
+    mask_bits = _need_cuda(mask_bits, 'mask_bits', torch.int32)
+    if mask_bits.dim() == 2:
+        mask_bits = mask_bits.unsqueeze(0)
+    req = np.ascontiguousarray(np.asarray(requests, np.int32).reshape(-1, 5))
+    n = len(req)
+    dev = mask_bits.device
+    ctx = get_context(dev)
+    yx = torch.zeros((n, int(max_px), 2), dtype=torch.int32, device=dev)
+    ln = torch.zeros(n, dtype=torch.int32, device=dev)
+    if n:
+        n_masks, H, _ = mask_bits.shape
+        ctx.check(ctx.lib.axb_trace_paths(ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), req.ctypes.data, n,
+                                          int(max_px), yx.data_ptr(), ln.data_ptr(), _stream()))
+    return yx, ln

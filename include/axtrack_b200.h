@@ -162,6 +162,22 @@ int axb_decode_nms_host(axb_ctx* ctx, const float* Y_host, const int32_t* tile_y
                         float* pre_conf_host, int32_t* pre_yx_host, int32_t* pre_cell_host, int32_t* n_pre_host,
                         float* conf_host, int32_t* yx_host, int32_t* keep_idx_host, int32_t* n_out_host);
 
+/* ---- path pixels -------------------------------------------------------
+ * Replaces utils._compute_astar_path (utils.py:351-390) -> pyastar2d.astar_path for the pairs
+ * whose PIXELS are wanted (the reference wraps them as a bool coo_matrix, utils.py:381-382; its
+ * own consumers only read getnnz()).  One request = (mask_idx, source y, source x, target y,
+ * target x), host int32 [n_req][5].  For every request the all-levels search records the
+ * direction each window cell was entered from and walks it back from the target:
+ *   path_len_dev  int32 [n_req]: pixels on the path L (start and goal included), 0 = None (the
+ *                 reference returns None: no path within max_px / Euclid >= max_px)
+ *   path_yx_dev   int32 [n_req][max_px][2]: (row, col) of the L pixels, start -> goal
+ * The path is A minimum-cost path under the reference's weights with exactly the reference's
+ * length and cost; which of the equal-cost paths is heap-tie dependent in the reference and is
+ * not reproduced.  Errors (start / goal outside the grid) arrive through axb_status. */
+int axb_trace_paths(axb_ctx* ctx, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
+                    const int32_t* req_host, int n_req, int max_px,
+                    int32_t* path_yx_dev, int32_t* path_len_dev, void* stream);
+
 /* ---- transition costs ------------------------------------------------------------------
  * Replaces the arithmetic of mincostflow_models.transition_model (mincostflow_models.py:100-119)
  * and the arc cost int(multi_factor * cost) of libmot's graph builder
