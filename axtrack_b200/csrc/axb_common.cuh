@@ -25,17 +25,17 @@ constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHas
 constexpr int kK2Threads = 256;       // one CTA (8 warps) per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
 // fast kernel (level 0 only): 3 CTAs per SM
-constexpr int kFastThreads = 128;     // fast kernels: one CTA (4 warps) per source search, one thread per frontier entry
+constexpr int kFastThreads = 96;     // fast kernels: one CTA (4 warps) per source search, one thread per frontier entry
 constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entries per buffer
 // dense window (every tile word of the folded diamond, 64.5 KB): 3 CTAs per SM
 constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory
 constexpr int kFastCtasPerSm = 3;
 // sparse window (only the non-zero tile words + a presence/base table): 8 CTAs per SM
-constexpr int kSparseWords = 4416;    // non-zero tile words a sparse window can hold (17.25 KB)
-constexpr int kSparseQCap = 256;
+constexpr int kSparseWords = 3936;    // non-zero tile words a sparse window can hold (15.4 KB)
+constexpr int kSparseQCap = 144;
 constexpr int kSparseHash = 512;
 constexpr int kSparseHashMaxLoad = 320;
-constexpr int kSparseCtasPerSm = 8;
+constexpr int kSparseCtasPerSm = 10;
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
@@ -73,12 +73,12 @@ inline size_t k2_fast_smem_bytes(int max_px) {      // dense window + queues + h
     return ((size_t)k2_tile_rows(max_px) * 128 + 4 * kFastQCap + kHashSize) * sizeof(uint32_t);
 }
 inline size_t k2_sparse_smem_bytes(int max_px) {    // packed words + (presence, base) per 32 tile columns + queues + hash
-    return ((size_t)kSparseWords + (size_t)k2_tile_rows(max_px) * 8 + 4 * kSparseQCap + kSparseHash) * sizeof(uint32_t);
+    return ((size_t)kSparseWords + (size_t)k2_tile_rows(max_px) * 8 + 4 * kSparseQCap) * sizeof(uint32_t);   // the target hash lives in the CTA's global scratch
 }
 inline size_t k2_gen_smem_bytes(int max_px) {
     return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
 }
-constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap;
+constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap + kSparseHash;
 constexpr size_t kTraceParBytes = (size_t)(AXB_MAX_PX + 1) * kRowBits;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
 

@@ -305,7 +305,9 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
     uint32_t* const WIN = smem;
     uint2* const PB = (uint2*)(WIN + (SPARSE ? kSparseWords : NR * kTC));
     uint2* const q0 = PB + (SPARSE ? NR * 4 : 0);          // [2][kNW][kSeg] (bits, key)
-    uint32_t* const hash = (uint32_t*)(q0 + 2 * C::kQCap);
+    // target hash: probed only for the few words flagged as holding a target, so the sparse
+    // kernel keeps it in the CTA's global scratch (L2) and spends the shared memory on residency
+    uint32_t* const hash = SPARSE ? gscr + kCandCap + 4 * (size_t)kFastGQCap : (uint32_t*)(q0 + 2 * C::kQCap);
     uint32_t* const cand = gscr;
     uint2* const gq0 = (uint2*)(gscr + kCandCap);          // [2][kNW][kGSeg] global overflow
     Chain& ch = ctl.ch;
@@ -434,7 +436,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             // ---- wavefronts: one thread per frontier entry (tile word key, frontier bits) ---------
             const uint32_t win_s = smem_u32(WIN);
             const uint32_t pb_s = smem_u32(PB);
-            const uint32_t hash_s = smem_u32(hash);
+            const uint32_t hash_s = SPARSE ? 0u : smem_u32(hash);
             const uint32_t q_s = smem_u32(q0);
             const uint32_t lastU = (uint32_t)(NR - 1);
             // shared address of tile word `key` (only when want != 0); want is cleared when the
