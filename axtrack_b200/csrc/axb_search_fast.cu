@@ -87,14 +87,16 @@ struct Win {
     int RW, NR, oy, ox;
 };
 
-// Tile word (tile row tr, tile column tc of the window) with the pixels outside the diamond
-// cleared.  hw_in / hw_out: half widths of the narrowest / widest image row of the tile row.
-__device__ __forceinline__ uint32_t window_tile(const Win& w, int tr, int tc, int hw_in, int hw_out) {
+// Where tile (tile row tr, tile column tc of the window) lives in the tiled mask and which of its
+// pixels lie inside the diamond; nullptr when none does.  hw_in / hw_out: half widths of the
+// narrowest / widest image row of the tile row.
+__device__ __forceinline__ const uint32_t* window_tile(const Win& w, int tr, int tc, int hw_in, int hw_out, uint32_t& m) {
     const int x0 = 8 * tc - w.ox;                       // dx of the tile's first pixel
-    if (x0 + 7 < -hw_out || x0 > hw_out) return 0u;
+    m = 0u;
+    if (x0 + 7 < -hw_out || x0 > hw_out) return nullptr;
     const int ty = w.ty0 + tr, tx = w.tx0 + tc;
-    if (ty < 0 || ty >= w.TH || tx < 0 || tx >= w.TWp) return 0u;
-    uint32_t m = 0xFFFFFFFFu;
+    if (ty < 0 || ty >= w.TH || tx < 0 || tx >= w.TWp) return nullptr;
+    m = 0xFFFFFFFFu;
     if (x0 < -hw_in || x0 + 7 > hw_in) {                // the diamond edge crosses the tile
         m = 0u;
         const int dy0 = 4 * tr - w.oy;
@@ -104,24 +106,25 @@ __device__ __forceinline__ uint32_t window_tile(const Win& w, int tr, int tc, in
             const int lo = max(-hw - x0, 0), hi = min(hw - x0, 7);
             if (hw >= 0 && lo <= hi) m |= (((0xFFu >> (7 - hi)) & (0xFFu << lo)) & 0xFFu) << (8 * r);
         }
-        if (m == 0u) return 0u;
+        if (m == 0u) return nullptr;
     }
-    return __ldg(w.tiles + (size_t)ty * w.TWp + tx) & m;
+    return w.tiles + (size_t)ty * w.TWp + tx;
 }
 
-// tile word of folded row fr, folded column col.  A folded column holds tile column col-64 or
+// The tile of folded row fr, folded column col.  A folded column holds tile column col-64 or
 // col+64 of the upper tile row and tile column col or col-128 of the lower one; at most one of
-// each pair lies inside the row's span, and the spans of the two halves never overlap.
-__device__ __forceinline__ uint32_t folded_tile(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l) {
+// each pair lies inside the row's span, and the spans of the two halves never overlap: at most
+// one source tile per folded word.
+__device__ __forceinline__ const uint32_t* folded_tile(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l, uint32_t& m) {
     int tc = col - 64;
     if (8 * tc - w.ox + 7 < -hwo_u) tc += 128;
-    uint32_t t = window_tile(w, fr - w.NR + 1, tc, hwi_u, hwo_u);
-    if (fr + 1 <= w.NR - 1) {
+    const uint32_t* ptr = window_tile(w, fr - w.NR + 1, tc, hwi_u, hwo_u, m);
+    if (!ptr && fr + 1 <= w.NR - 1) {
         tc = col;
         if (8 * tc - w.ox > hwo_l) tc -= 128;
-        t |= window_tile(w, fr + 1, tc, hwi_l, hwo_l);
+        ptr = window_tile(w, fr + 1, tc, hwi_l, hwo_l, m);
     }
-    return t;
+    return ptr;
 }
 
 __device__ __forceinline__ void row_half_widths(const Win& w, int tr, int& hw_in, int& hw_out) {
@@ -256,9 +259,15 @@ __device__ __forceinline__ void stage_window(const Win& w, uint32_t* WIN, uint2*
         int hwi_u, hwo_u, hwi_l, hwo_l;
         row_half_widths(w, fr - w.NR + 1, hwi_u, hwo_u);
         row_half_widths(w, fr + 1, hwi_l, hwo_l);
-        uint32_t t[4];
+        // addresses and diamond masks of the four tiles first, then the four loads back to back
+        const uint32_t* src[4];
+        uint32_t msk[4], t[4];
         #pragma unroll
-        for (int g = 0; g < 4; ++g) t[g] = folded_tile(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l);
+        for (int g = 0; g < 4; ++g) src[g] = folded_tile(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l, msk[g]);
+        #pragma unroll
+        for (int g = 0; g < 4; ++g) t[g] = src[g] ? __ldg(src[g]) : 0u;
+        #pragma unroll
+        for (int g = 0; g < 4; ++g) t[g] &= msk[g];
         if (!SPARSE) {
             #pragma unroll
             for (int g = 0; g < 4; ++g) WIN[fr * kTC + 32 * g + lane] = t[g];
