@@ -111,10 +111,13 @@ __device__ __forceinline__ const uint32_t* window_tile(const Win& w, int tr, int
     return w.tiles + (size_t)ty * w.TWp + tx;
 }
 
-// The tile of folded row fr, folded column col.  A folded column holds tile column col-64 or
-// col+64 of the upper tile row and tile column col or col-128 of the lower one; at most one of
-// each pair lies inside the row's span, and the spans of the two halves never overlap: at most
-// one source tile per folded word.
+// The tile of folded row fr, folded column col, for max_px <= kOneTileMaxPx.  A folded column
+// holds tile column col-64 or col+64 of the upper tile row and tile column col or col-128 of the
+// lower one.  An image row spans at most 2*504+1 pixels, i.e. at most 128 tile columns at any
+// alignment, so at most one of each pair lies inside the row's span; and the spans of the two
+// halves are at least 8 pixels apart on the circle, so at most one source tile per folded word.
+// Above that radius a row can wrap onto its own first tile and the halves can meet inside one
+// word (the pixels stay disjoint): folded_word_wide ORs all four candidates.
 __device__ __forceinline__ const uint32_t* folded_tile(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l, uint32_t& m) {
     int tc = col - 64;
     if (8 * tc - w.ox + 7 < -hwo_u) tc += 128;
@@ -125,6 +128,20 @@ __device__ __forceinline__ const uint32_t* folded_tile(const Win& w, int fr, int
         ptr = window_tile(w, fr + 1, tc, hwi_l, hwo_l, m);
     }
     return ptr;
+}
+
+constexpr int kOneTileMaxPx = 504;
+__device__ __forceinline__ uint32_t folded_word_wide(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l) {
+    uint32_t t = 0u, m;
+    #pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+        const bool upper = k < 2;
+        if (!upper && fr + 1 > w.NR - 1) break;
+        const int tc = upper ? col - 64 + 128 * k : col - 128 * (k - 2);
+        const uint32_t* src = upper ? window_tile(w, fr - w.NR + 1, tc, hwi_u, hwo_u, m) : window_tile(w, fr + 1, tc, hwi_l, hwo_l, m);
+        if (src) t |= __ldg(src) & m;
+    }
+    return t;
 }
 
 __device__ __forceinline__ void row_half_widths(const Win& w, int tr, int& hw_in, int& hw_out) {
@@ -262,12 +279,17 @@ __device__ __forceinline__ void stage_window(const Win& w, uint32_t* WIN, uint2*
         // addresses and diamond masks of the four tiles first, then the four loads back to back
         const uint32_t* src[4];
         uint32_t msk[4], t[4];
-        #pragma unroll
-        for (int g = 0; g < 4; ++g) src[g] = folded_tile(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l, msk[g]);
-        #pragma unroll
-        for (int g = 0; g < 4; ++g) t[g] = src[g] ? __ldg(src[g]) : 0u;
-        #pragma unroll
-        for (int g = 0; g < 4; ++g) t[g] &= msk[g];
+        if (w.RW <= kOneTileMaxPx) {
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) src[g] = folded_tile(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l, msk[g]);
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) t[g] = src[g] ? __ldg(src[g]) : 0u;
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) t[g] &= msk[g];
+        } else {
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) t[g] = folded_word_wide(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l);
+        }
         if (!SPARSE) {
             #pragma unroll
             for (int g = 0; g < 4; ++g) WIN[fr * kTC + 32 * g + lane] = t[g];

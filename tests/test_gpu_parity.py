@@ -333,6 +333,40 @@ def test_sparse_window_multi_pass_and_dense_fallback(cuda):
 
 
 @pytest.mark.gpu
+def test_window_rim_at_largest_radii(cuda):
+    """max_px > 504: the two halves of a folded window row come closer than one tile, so one folded
+    tile word holds rim pixels of an upper and of a lower image row.  Targets on and just inside the
+    rim of the diamond (hop max_px, max_px-1, ...) on a comb mask (sparse windows) and on an open
+    field (dense windows), sources at every (x & 31, y & 3) alignment class that matters."""
+    H, W = 1100, 1200
+    for max_px in (505, 508, 511):
+        for field in ('comb', 'open'):
+            srcs = [(548 + k % 4, 590 + 5 * k) for k in range(8)] if field == 'comb' else [(549, 601), (550, 622)]
+            for sy, sx in srcs:
+                if field == 'comb':
+                    mask = np.zeros((H, W), np.uint8)
+                    mask[sy % 12::12, :] = 1          # rows every 12 through the source row
+                    mask[:, sx] = 1
+                else:
+                    mask = np.ones((H, W), np.uint8)
+                rows = np.arange(sy % 12, H, 12) if field == 'comb' else np.arange(max(sy - max_px, 0), min(sy + max_px + 1, H), 7)
+                dst = []
+                for y in rows:
+                    hw = max_px - abs(int(y) - sy)
+                    if hw < 0:
+                        continue
+                    for side in (-1, 1):
+                        for inward in range(0, 10, 1 if field == 'comb' else 3):
+                            x = sx + side * (hw - inward)
+                            if hw - inward >= 0 and 0 <= x < W:
+                                dst.append((y, x))
+                src = np.array([[sy, sx]], np.int32)
+                dst = np.array(dst, np.int32)
+                _check(_gpu_cost(cuda, mask, src, dst, max_px), oracle.cost_matrix_rule(mask, src, dst, max_px),
+                       (field, max_px, sy, sx))
+
+
+@pytest.mark.gpu
 def test_decode_nms_8192_frames(cuda):
     """BASELINE configs[4] shape: 8192x8192 frames = 256 tiles x 12x12 cells, thousands of candidates
     per frame (the sort leaves shared memory), several frames per launch; survivor indices,
