@@ -111,37 +111,36 @@ __device__ __forceinline__ const uint32_t* window_tile(const Win& w, int tr, int
     return w.tiles + (size_t)ty * w.TWp + tx;
 }
 
-// The tile of folded row fr, folded column col, for max_px <= kOneTileMaxPx.  A folded column
-// holds tile column col-64 or col+64 of the upper tile row and tile column col or col-128 of the
-// lower one.  An image row spans at most 2*504+1 pixels, i.e. at most 128 tile columns at any
-// alignment, so at most one of each pair lies inside the row's span; and the spans of the two
-// halves are at least 8 pixels apart on the circle, so at most one source tile per folded word.
-// Above that radius a row can wrap onto its own first tile and the halves can meet inside one
-// word (the pixels stay disjoint): folded_word_wide ORs all four candidates.
-__device__ __forceinline__ const uint32_t* folded_tile(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l, uint32_t& m) {
-    int tc = col - 64;
-    if (8 * tc - w.ox + 7 < -hwo_u) tc += 128;
-    const uint32_t* ptr = window_tile(w, fr - w.NR + 1, tc, hwi_u, hwo_u, m);
-    if (!ptr && fr + 1 <= w.NR - 1) {
-        tc = col;
-        if (8 * tc - w.ox > hwo_l) tc -= 128;
-        ptr = window_tile(w, fr + 1, tc, hwi_l, hwo_l, m);
-    }
-    return ptr;
+// Four adjacent tiles (a 16-byte aligned quad: 32 x 4 pixels) of window tile row tr starting at
+// tile column tcq (a multiple of 4): where they live in the tiled mask, or nullptr when no pixel
+// of the quad lies inside the diamond or the image.  x0 = dx of the quad's first pixel.
+__device__ __forceinline__ const uint4* window_quad(const Win& w, int tr, int tcq, int hw_out, int& x0) {
+    x0 = 8 * tcq - w.ox;
+    if (x0 + 31 < -hw_out || x0 > hw_out) return nullptr;
+    const int ty = w.ty0 + tr, tx = w.tx0 + tcq;        // tx0, tcq and TWp are multiples of 4
+    if (ty < 0 || ty >= w.TH || tx < 0 || tx >= w.TWp) return nullptr;
+    return reinterpret_cast<const uint4*>(w.tiles + (size_t)ty * w.TWp + tx);
 }
 
-constexpr int kOneTileMaxPx = 504;
-__device__ __forceinline__ uint32_t folded_word_wide(const Win& w, int fr, int col, int hwi_u, int hwo_u, int hwi_l, int hwo_l) {
-    uint32_t t = 0u, m;
-    #pragma unroll 1
-    for (int k = 0; k < 4; ++k) {
-        const bool upper = k < 2;
-        if (!upper && fr + 1 > w.NR - 1) break;
-        const int tc = upper ? col - 64 + 128 * k : col - 128 * (k - 2);
-        const uint32_t* src = upper ? window_tile(w, fr - w.NR + 1, tc, hwi_u, hwo_u, m) : window_tile(w, fr + 1, tc, hwi_l, hwo_l, m);
-        if (src) t |= __ldg(src) & m;
+// Clear the pixels of a loaded quad that lie outside the diamond (only when its edge crosses the quad).
+__device__ __forceinline__ void clip_quad(const Win& w, int tr, int x0, int hw_in, uint4& v) {
+    if (x0 >= -hw_in && x0 + 31 <= hw_in) return;
+    const int dy0 = 4 * tr - w.oy;
+    uint32_t rm[4];                                     // the quad's 32 pixels of each of its 4 image rows
+    #pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int hw = w.RW - abs(dy0 + r);
+        const int lo = max(-hw - x0, 0), hi = min(hw - x0, 31);
+        rm[r] = (hw >= 0 && lo <= hi) ? ((0xFFFFFFFFu >> (31 - hi)) & (0xFFFFFFFFu << lo)) : 0u;
     }
-    return t;
+    uint32_t m[4];                                      // tile k = byte k of the four rows
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t lo = __byte_perm(rm[0], rm[1], k | ((4 + k) << 4));
+        const uint32_t hi = __byte_perm(rm[2], rm[3], k | ((4 + k) << 4));
+        m[k] = __byte_perm(lo, hi, 0x5410);
+    }
+    v.x &= m[0]; v.y &= m[1]; v.z &= m[2]; v.w &= m[3];
 }
 
 __device__ __forceinline__ void row_half_widths(const Win& w, int tr, int& hw_in, int& hw_out) {
@@ -264,50 +263,61 @@ __device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash
     return n;
 }
 
-// Stage the folded window from the tiled mask: one warp per folded row, four passes of 32 tile
-// columns, lane = tile column.  Dense: WIN[fr*128 + col].  Sparse: the non-zero words of the 32
-// columns are packed behind each other, PB[fr*4 + g] = (presence bits, index of the first one);
-// groups are allocated in any order (one atomicAdd per folded row).  Returns via ctl.alloc.
+// Stage the folded window from the tiled mask: one warp per folded row, lane = a quad of four
+// folded tile columns (4*lane .. 4*lane+3).  A folded column holds tile column col-64 or col+64
+// of the upper tile row and tile column col or col-128 of the lower one: the four candidate quads
+// are loaded as 16-byte words, clipped to the diamond and ORed.  (Up to max_px = 504 at most one
+// candidate per half is inside the row's span and at most one per folded word; above that a row
+// can wrap onto its own first tile and the two halves can meet inside one word, but the pixels of
+// the candidates stay disjoint, so the OR is exact at every radius.)
+// Dense: WIN[fr*128 + col].  Sparse: the non-zero words of each group of 32 columns are packed
+// behind each other in column order, PB[fr*4 + g] = (presence bits, index of the first one);
+// the groups of a folded row are allocated together (one atomicAdd per row), rows in any order.
 template <bool SPARSE>
-__device__ __forceinline__ void stage_window(const Win& w, uint32_t* WIN, uint2* PB, Ctl& ctl) {
+__device__ __noinline__ void stage_window(const Win w, uint32_t* WIN, uint2* PB, Ctl& ctl) {
     const int lane = threadIdx.x & 31;
-    const uint32_t lt = lanemask_lt();
     for (int fr = threadIdx.x >> 5; fr < w.NR; fr += kNW) {
+        const int tr_u = fr - w.NR + 1, tr_l = fr + 1;
         int hwi_u, hwo_u, hwi_l, hwo_l;
-        row_half_widths(w, fr - w.NR + 1, hwi_u, hwo_u);
-        row_half_widths(w, fr + 1, hwi_l, hwo_l);
-        // addresses and diamond masks of the four tiles first, then the four loads back to back
-        const uint32_t* src[4];
-        uint32_t msk[4], t[4];
-        if (w.RW <= kOneTileMaxPx) {
-            #pragma unroll
-            for (int g = 0; g < 4; ++g) src[g] = folded_tile(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l, msk[g]);
-            #pragma unroll
-            for (int g = 0; g < 4; ++g) t[g] = src[g] ? __ldg(src[g]) : 0u;
-            #pragma unroll
-            for (int g = 0; g < 4; ++g) t[g] &= msk[g];
-        } else {
-            #pragma unroll
-            for (int g = 0; g < 4; ++g) t[g] = folded_word_wide(w, fr, 32 * g + lane, hwi_u, hwo_u, hwi_l, hwo_l);
+        row_half_widths(w, tr_u, hwi_u, hwo_u);
+        row_half_widths(w, tr_l, hwi_l, hwo_l);
+        if (tr_l > w.NR - 1) hwo_l = -64;               // no lower tile row: nothing in span
+        uint32_t t[4] = {0u, 0u, 0u, 0u};
+        #pragma unroll
+        for (int h = 0; h < 2; ++h) {                   // upper, lower: addresses, loads back to back, clipping
+            const int tr = h ? tr_l : tr_u, hwi = h ? hwi_l : hwi_u, hwo = h ? hwo_l : hwo_u;
+            int xa, xb;
+            const uint4* sa = window_quad(w, tr, h ? 4 * lane : 4 * lane - 64, hwo, xa);
+            const uint4* sb = window_quad(w, tr, h ? 4 * lane - 128 : 4 * lane + 64, hwo, xb);
+            uint4 va = sa ? __ldg(sa) : make_uint4(0u, 0u, 0u, 0u);
+            uint4 vb = sb ? __ldg(sb) : make_uint4(0u, 0u, 0u, 0u);
+            if (sa) clip_quad(w, tr, xa, hwi, va);
+            if (sb) clip_quad(w, tr, xb, hwi, vb);
+            t[0] |= va.x | vb.x; t[1] |= va.y | vb.y; t[2] |= va.z | vb.z; t[3] |= va.w | vb.w;
         }
         if (!SPARSE) {
-            #pragma unroll
-            for (int g = 0; g < 4; ++g) WIN[fr * kTC + 32 * g + lane] = t[g];
+            *reinterpret_cast<uint4*>(WIN + fr * kTC + 4 * lane) = make_uint4(t[0], t[1], t[2], t[3]);
         } else {
+            // presence bits of my group of 32 columns (8 lanes x 4 columns)
+            const int sh = 4 * (lane & 7), grp = lane >> 3;
+            const uint32_t nib = (t[0] != 0u ? 1u : 0u) | (t[1] != 0u ? 2u : 0u) | (t[2] != 0u ? 4u : 0u) | (t[3] != 0u ? 8u : 0u);
             uint32_t pr[4];
-            int cnt[4];
             #pragma unroll
-            for (int g = 0; g < 4; ++g) { pr[g] = __ballot_sync(kFull, t[g] != 0u); cnt[g] = __popc(pr[g]); }
+            for (int g = 0; g < 4; ++g) pr[g] = __reduce_or_sync(kFull, grp == g ? nib << sh : 0u);
+            const int c0 = __popc(pr[0]), c1 = __popc(pr[1]), c2 = __popc(pr[2]), c3 = __popc(pr[3]);
             int base = 0;
-            if (lane == 0) base = atomicAdd(&ctl.alloc, cnt[0] + cnt[1] + cnt[2] + cnt[3]);
+            if (lane == 0) base = atomicAdd(&ctl.alloc, c0 + c1 + c2 + c3);
             base = __shfl_sync(kFull, base, 0);
+            const uint32_t mypr = grp == 0 ? pr[0] : grp == 1 ? pr[1] : grp == 2 ? pr[2] : pr[3];
+            const int gbase = base + (grp > 0 ? c0 : 0) + (grp > 1 ? c1 : 0) + (grp > 2 ? c2 : 0);
+            if ((lane & 7) == 0) PB[fr * 4 + grp] = make_uint2(mypr, (uint32_t)gbase);
+            int idx = gbase + __popc(mypr & ((1u << sh) - 1u));
             #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                if (lane == g) PB[fr * 4 + g] = make_uint2(pr[g], (uint32_t)base);
-                const int idx = base + __popc(pr[g] & lt);
-                if (t[g] != 0u && idx < kSparseWords) WIN[idx] = t[g];
-                base += cnt[g];
-            }
+            for (int k = 0; k < 4; ++k)
+                if (t[k] != 0u) {
+                    if (idx < kSparseWords) WIN[idx] = t[k];
+                    ++idx;
+                }
         }
     }
 }
