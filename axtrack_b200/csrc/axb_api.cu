@@ -182,7 +182,7 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     p.mask_tiles = c->k2_tiles; p.TH = TH; p.TWp = 4 * Wp;
     p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs;
     p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
-    p.max_px = max_px; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
+    p.max_px = max_px; p.hash_smem = 0; p.sparse_words = axb::kSparseWords; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;

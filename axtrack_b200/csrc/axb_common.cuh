@@ -53,6 +53,8 @@ struct K2Params {
     const int* all_prefix;       // [n_pairs+1] exclusive prefix of n_src over all pairs (error order)
     const int* next_same;        // [n_pairs] next pair with the same (mask, sources), or -1
     int max_px;
+    int hash_smem;               // k2_sparse_kernel: target hash in shared memory (set by launch_k2_sparse)
+    int sparse_words;            // k2_sparse_kernel: non-zero tile words a window can hold (set by launch_k2_sparse)
     int32_t* path_len;
     uint8_t* unreachable;
     float* wcost;

@@ -274,7 +274,7 @@ __device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash
 // behind each other in column order, PB[fr*4 + g] = (presence bits, index of the first one);
 // the groups of a folded row are allocated together (one atomicAdd per row), rows in any order.
 template <bool SPARSE>
-__device__ __noinline__ void stage_window(const Win w, uint32_t* WIN, uint2* PB, Ctl& ctl) {
+__device__ __noinline__ void stage_window(const Win w, uint32_t* WIN, uint2* PB, Ctl& ctl, const int cap_words) {
     const int lane = threadIdx.x & 31;
     for (int fr = threadIdx.x >> 5; fr < w.NR; fr += kNW) {
         const int tr_u = fr - w.NR + 1, tr_l = fr + 1;
@@ -315,7 +315,7 @@ __device__ __noinline__ void stage_window(const Win w, uint32_t* WIN, uint2* PB,
             #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (t[k] != 0u) {
-                    if (idx < kSparseWords) WIN[idx] = t[k];
+                    if (idx < cap_words) WIN[idx] = t[k];
                     ++idx;
                 }
         }
@@ -344,11 +344,12 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
 
     // shared memory: window words | (sparse) presence/base table | two frontier buffers | target hash
     uint32_t* const WIN = smem;
-    uint2* const PB = (uint2*)(WIN + (SPARSE ? kSparseWords : NR * kTC));
+    uint2* const PB = (uint2*)(WIN + (SPARSE ? p.sparse_words : NR * kTC));
     uint2* const q0 = PB + (SPARSE ? NR * 4 : 0);          // [2][kNW][kSeg] (bits, key)
     // target hash: probed only for the few words flagged as holding a target, so the sparse
     // kernel keeps it in the CTA's global scratch (L2) and spends the shared memory on residency
-    uint32_t* const hash = SPARSE ? gscr + kCandCap + 4 * (size_t)kFastGQCap : (uint32_t*)(q0 + 2 * C::kQCap);
+    // (unless the launch is too small to fill the SMs: then latency counts, p.hash_smem)
+    uint32_t* const hash = SPARSE && !p.hash_smem ? gscr + kCandCap + 4 * (size_t)kFastGQCap : (uint32_t*)(q0 + 2 * C::kQCap);
     uint32_t* const cand = gscr;
     uint2* const gq0 = (uint2*)(gscr + kCandCap);          // [2][kNW][kGSeg] global overflow
     Chain& ch = ctl.ch;
@@ -444,10 +445,10 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
         const int ncand = ctl.ncand;
         if (ncand > 0) {
             AXB_T(0, tclk);
-            stage_window<SPARSE>(w, WIN, PB, ctl);
+            stage_window<SPARSE>(w, WIN, PB, ctl, p.sparse_words);
             __syncthreads();
             AXB_T(1, tclk);
-            if (SPARSE && ctl.alloc > kSparseWords) return kItemToDense;
+            if (SPARSE && ctl.alloc > p.sparse_words) return kItemToDense;
             if (SPARSE) {              // flag the tile-word pairs that hold a target: bits 16.. of PB[].y
                 for (int i = tid; i < HASH; i += NT) {
                     const uint32_t e = hash[i];
@@ -648,10 +649,32 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
     static unsigned long long attr_set = 0ull;
     if (first_use_on_device(attr_set)) {
-        cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_sparse_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
         cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     }
-    k2_sparse_kernel<<<grid, kFastThreads, k2_sparse_smem_bytes(p.max_px), stream>>>(p);
+    // A launch that leaves at least half of the CTA slots empty is latency bound and has shared
+    // memory to spare: the target hash moves from the CTA's global scratch into shared memory and
+    // the window capacity grows to what the launch's residency leaves (up to the whole folded
+    // diamond, so that no window needs the dense kernel's second pass).
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    K2Params q = p;
+    q.hash_smem = 0;
+    q.sparse_words = kSparseWords;
+    size_t smem = k2_sparse_smem_bytes(p.max_px);
+    if (2 * grid <= sms * kSparseCtasPerSm) {
+        const int per_sm = (grid + sms - 1) / sms;
+        const size_t fixed = smem - (size_t)kSparseWords * sizeof(uint32_t) + kSparseHash * sizeof(uint32_t);
+        const size_t budget = (size_t)227 * 1024 / per_sm - 1024;
+        const size_t full = (size_t)k2_tile_rows(p.max_px) * 128;
+        size_t words = (budget - fixed) / sizeof(uint32_t) & ~(size_t)3;
+        if (words > full) words = full;
+        q.hash_smem = 1;
+        q.sparse_words = (int)words;
+        smem = fixed + words * sizeof(uint32_t);
+    }
+    k2_sparse_kernel<<<grid, kFastThreads, smem, stream>>>(q);
 }
 
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {

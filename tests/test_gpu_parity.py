@@ -330,6 +330,11 @@ def test_sparse_window_multi_pass_and_dense_fallback(cuda):
     dst = np.stack([rng.integers(0, H, 300), rng.integers(0, W, 300)], 1).astype(np.int32)
     for max_px in (500, 511, 130):
         _check(_gpu_cost(cuda, ones, src, dst, max_px), oracle.cost_matrix_rule(ones, src, dst, max_px), ('dense', max_px))
+    # (c) a launch that fills the CTA slots keeps the small sparse windows (a small launch grows them
+    # to what its residency leaves): 800 open-field sources at radius 300 overflow them -> dense kernel
+    src = np.stack([rng.integers(0, H, 800), rng.integers(0, W, 800)], 1).astype(np.int32)
+    dst = np.stack([rng.integers(0, H, 60), rng.integers(0, W, 60)], 1).astype(np.int32)
+    _check(_gpu_cost(cuda, ones, src, dst, 300), oracle.cost_matrix_rule(ones, src, dst, 300), 'dense, full launch')
 
 
 @pytest.mark.gpu
