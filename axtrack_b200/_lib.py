@@ -18,7 +18,7 @@ ERR_BAD_WEIGHT = -4
 ERR_BAD_ARG = -5
 ERR_CAPACITY = -6
 ERR_UNSUPPORTED_WEIGHT = -7
-MAX_PX = 511
+MAX_PX = 1023
 
 #: every symbol include/axtrack_b200.h declares
 SYMBOLS = ('axb_create', 'axb_destroy', 'axb_last_error', 'axb_version', 'axb_launch_count',

@@ -21,6 +21,8 @@ struct axb_ctx {
     // K2
     uint32_t* k2_fast_scratch = nullptr;   int k2_fast_ctas = 0;
     uint32_t* k2_gen_scratch = nullptr;    int k2_gen_ctas = 0;
+    uint32_t* k2_wide_scratch = nullptr;   // max_px > 511: per general CTA kGenScratchWordsWide (allocated on first use)
+    uint8_t* trace_par_wide = nullptr;
     int* counters = nullptr;
     int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;   // [work | all | next] x prefix_cap
     int* gen_list = nullptr;          size_t gen_list_bytes = 0;
@@ -120,7 +122,7 @@ void axb_destroy(axb_ctx* c) {
     cudaDeviceSynchronize();
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
-    cudaFree(c->trace_par); cudaFree(c->trace_iota);
+    cudaFree(c->trace_par); cudaFree(c->trace_iota); cudaFree(c->k2_wide_scratch); cudaFree(c->trace_par_wide);
     cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
     cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1);
@@ -171,7 +173,10 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     const int Wp = (W + 31) / 32, TH = (H + 3) / 4;
     rc = grow(c, &c->k2_tiles, &c->k2_tiles_bytes, (size_t)n_masks * TH * Wp * 4 * sizeof(uint32_t));
     if (rc != AXB_OK) return rc;
-    axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
+    const bool wide = max_px > axb::kFastMaxPx;
+    if (wide && !c->k2_wide_scratch)
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kGenScratchWordsWide * sizeof(uint32_t)));
+    if (!wide) axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
     int* const work_prefix = c->prefix_dev;
     int* const all_prefix = c->prefix_dev + c->prefix_cap;
     int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
@@ -183,9 +188,16 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs;
     p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
     p.max_px = max_px; p.hash_smem = 0; p.sparse_words = axb::kSparseWords; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
-    p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
+    p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = wide ? c->k2_wide_scratch : c->k2_gen_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
+    if (wide) {      // beyond the tile-word kernels' window: every source goes through the wide all-levels kernel
+        axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
+        axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
+        c->launches += 3;
+        AXB_CUDA(c, cudaGetLastError());
+        return AXB_OK;
+    }
     axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
     axb::launch_k2_fast(p, std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src)), s);
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
@@ -375,7 +387,11 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     cudaStream_t s = (cudaStream_t)stream;
     int rc = ensure_k2(c, n_req, n_req);
     if (rc != AXB_OK) return rc;
-    if (!c->trace_par) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par, (size_t)c->k2_gen_ctas * axb::kTraceParBytes));
+    const bool wide = max_px > axb::kFastMaxPx;
+    if (!wide && !c->trace_par) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par, (size_t)c->k2_gen_ctas * axb::kTraceParBytes));
+    if (wide && !c->trace_par_wide) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par_wide, (size_t)c->k2_gen_ctas * axb::kTraceParBytesWide));
+    if (wide && !c->k2_wide_scratch)
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kGenScratchWordsWide * sizeof(uint32_t)));
     // one 1 x 1 frame pair per request: detections rows 2i (source), 2i+1 (target)
     std::vector<int32_t> dets((size_t)n_req * 4);
     std::vector<axb_pair_desc> pairs((size_t)n_req);
@@ -410,9 +426,9 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     p.dets_yx = c->st_dets; p.pairs = c->st_pairs; p.n_pairs = n_req;
     p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
     p.max_px = max_px; p.path_len = c->st_plen; p.unreachable = c->st_unr; p.wcost = nullptr;
-    p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = c->k2_gen_scratch;
+    p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = wide ? c->k2_wide_scratch : c->k2_gen_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
-    p.trace_par = c->trace_par; p.trace_yx = path_yx_dev; p.trace_len = path_len_dev;
+    p.trace_par = wide ? c->trace_par_wide : c->trace_par; p.trace_yx = path_yx_dev; p.trace_len = path_len_dev;
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, n_req)), s);
     c->launches += 2;
     AXB_CUDA(c, cudaGetLastError());

@@ -24,6 +24,9 @@ constexpr int kHashMaxLoad = 640;     // candidates per search pass
 constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
 constexpr int kK2Threads = 256;       // one CTA (8 warps) per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
+constexpr int kSeedCalWide = 1024;
+constexpr int kFastMaxPx = 511;       // largest radius of the 1024-column folded window (tile-word kernels, shared-memory bitmaps)
+static_assert(AXB_MAX_PX == 1023, "wide layout: 2048-bit folded rows");
 // fast kernel (level 0 only): 3 CTAs per SM
 constexpr int kFastThreads = 96;     // fast kernels: one CTA (4 warps) per source search, one thread per frontier entry
 constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entries per buffer
@@ -39,6 +42,7 @@ constexpr int kSparseCtasPerSm = 10;
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
+constexpr int kGCapWide = 1 << 21;
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;
 
 struct K2Params {
@@ -80,9 +84,14 @@ inline size_t k2_sparse_smem_bytes(int max_px) {    // packed words + (presence,
 inline size_t k2_gen_smem_bytes(int max_px) {
     return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
 }
+inline size_t k2_gen_wide_smem_bytes() {            // bitmaps in global scratch
+    return (2 * (size_t)kGenQCap + kHashSize + 2 * kSeedCalWide) * sizeof(uint32_t);
+}
 constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap + kSparseHash;
-constexpr size_t kTraceParBytes = (size_t)(AXB_MAX_PX + 1) * kRowBits;
+constexpr size_t kTraceParBytes = (size_t)(kFastMaxPx + 1) * kRowBits;
+constexpr size_t kTraceParBytesWide = (size_t)(AXB_MAX_PX + 1) * 2 * kRowBits;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
+constexpr size_t kGenScratchWordsWide = (size_t)kCandCap + 4 * (size_t)kGCapWide + 2 * (size_t)(AXB_MAX_PX + 1) * 2 * kRowWords;
 
 // Function attributes are per device: true the first time the calling thread's current device is
 // seen for `flags` (one 64-bit word per kernel), so that the opt-in shared-memory size is set once
@@ -101,7 +110,8 @@ void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, i
 void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
-void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);
+void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);     // max_px > kFastMaxPx: the wide kernel
+void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);
 void launch_pack_mask_f32(const float* w, int n_masks, int H, int W, uint32_t* bits,
                           unsigned long long* err_flags, cudaStream_t s);

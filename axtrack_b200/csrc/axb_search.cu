@@ -61,27 +61,42 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
     return m;
 }
 
-// queue entry: (dy + 512) << 11 | (cx + 512); cx = x - (sx & ~31) in [-511, 542]
-__device__ __forceinline__ uint32_t pack_cell(int dy, int cx) {
-    return ((uint32_t)(dy + 512) << 11) | (uint32_t)(cx + 512);
+// Window geometry of the all-levels kernel.  Up to max_px = 511 the folded rows are 1024 bits and
+// both bitmaps live in shared memory; the WIDE variant (512 <= max_px <= 1023: the reference honours
+// any max_px_assoc_dist, AxonDetections.py:623-625,736) folds on 2048-bit rows and keeps the bitmaps
+// in the CTA's global scratch (512 KB, L2 resident).
+template <bool WIDE> struct Geo {
+    static constexpr int LOG = WIDE ? 11 : 10;       // log2(bits of a folded row)
+    static constexpr int RB = 1 << LOG, RWD = RB / 32, HALF = RB / 2;
+    static constexpr int CSH = LOG + 1;              // queue entry: (dy + HALF) << CSH | (cx + HALF)
+    static constexpr int ESH = WIDE ? 11 : 13;       // hash entry: cell index << ESH | candidate slot
+    static constexpr int CAL = WIDE ? kSeedCalWide : kSeedCal;
+    static constexpr int GQ = WIDE ? kGCapWide : kGCap;
+    static constexpr size_t SCRATCH = WIDE ? kGenScratchWordsWide : kGenScratchWords;
+    static constexpr size_t PAR = WIDE ? kTraceParBytesWide : kTraceParBytes;
+};
+static_assert(kCandCap <= (1 << Geo<true>::ESH) && kCandCap <= (1 << Geo<false>::ESH), "hash entries keep ESH bits of candidate slot");
+
+// queue entry; cx = x - (sx & ~31) in [-(HALF-1), HALF+30]
+template <bool WIDE> __device__ __forceinline__ uint32_t pack_cell(int dy, int cx) {
+    return ((uint32_t)(dy + Geo<WIDE>::HALF) << Geo<WIDE>::CSH) | (uint32_t)(cx + Geo<WIDE>::HALF);
 }
 
-// logical cell index of the folded window: row * 1024 + column (the hash key of a target)
-__device__ __forceinline__ int fold_index(int dy, int cx, int RW) {
+// logical cell index of the folded window: row * RB + column (the hash key of a target)
+template <bool WIDE> __device__ __forceinline__ int fold_index(int dy, int cx, int RW) {
     const int row = dy <= 0 ? dy + RW : dy - 1;
-    const int col = (cx + (dy <= 0 ? 512 : 0)) & (kRowBits - 1);
-    return row * kRowBits + col;
+    const int col = (cx + (dy <= 0 ? Geo<WIDE>::HALF : 0)) & (Geo<WIDE>::RB - 1);
+    return row * Geo<WIDE>::RB + col;
 }
 
-// shared-memory word of a logical cell index: the 32 words of row r are rotated by r
-__device__ __forceinline__ int phys_word(int idx) {
-    const int row = idx >> 10;
-    return (row << 5) | (((idx >> 5) + row) & 31);
+// bitmap word of a logical cell index: the words of row r are rotated by r (shared-memory banks)
+template <bool WIDE> __device__ __forceinline__ int phys_word(int idx) {
+    const int row = idx >> Geo<WIDE>::LOG;
+    return row * Geo<WIDE>::RWD + (((idx >> 5) + row) & (Geo<WIDE>::RWD - 1));
 }
 
 __device__ __forceinline__ uint32_t hash_slot(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
 static_assert(kHashSize == 1024, "hash_slot keeps 10 bits");
-static_assert(kCandCap <= 8192, "hash entries keep 13 bits of candidate slot");
 
 struct Src {
     const uint32_t* mbits;
@@ -98,37 +113,42 @@ __device__ __forceinline__ void gather(const Src& s, int y, int iw, int xlo, int
     bg |= ~m & valid;
 }
 
-// Stage the folded window: one warp per folded row, lane = logical word of the row.  One shared
-// word is one aligned word of the packed mask: the upper half (dy <= 0) of folded row r sits at
-// columns cx+512, the lower half (dy = r+1) at columns cx (mod 1024); only lane 0 / lane 16 can
-// see a second, wrapped word of the same half.
-template <bool GEN, int NT>
+// Stage the folded window: one warp per folded row, lane = logical word of the row (two passes
+// for the 64-word rows of the WIDE layout).  One bitmap word is one aligned word of the packed
+// mask: the upper half (dy <= 0) of folded row r sits at columns cx+HALF, the lower half
+// (dy = r+1) at columns cx (mod RB); only word 0 / word RWD/2 can see a second, wrapped word of
+// the same half.
+template <bool GEN, int NT, bool WIDE>
 __device__ __forceinline__ void stage_window(const Src& s, uint32_t* OF, uint32_t* OB) {
+    constexpr int RWD = Geo<WIDE>::RWD;
     const int RW = s.RW;
     const int lane = threadIdx.x & 31;
     #pragma unroll 2
     for (int r = threadIdx.x >> 5; r <= RW; r += NT / 32) {
-        uint32_t fg = 0, bg = 0;
-        {
-            const int y = s.sy + r - RW;                       // upper half, half width r
-            if (y >= 0 && y < s.H) {
-                const int xlo = max(0, s.sx - r), xhi = min(s.W - 1, s.sx + r);
-                gather(s, y, s.iw0 - 16 + lane, xlo, xhi, fg, bg);
-                if (lane == 0) gather(s, y, s.iw0 + 16, xlo, xhi, fg, bg);
+        #pragma unroll
+        for (int wl = lane; wl < RWD; wl += 32) {
+            uint32_t fg = 0, bg = 0;
+            {
+                const int y = s.sy + r - RW;                       // upper half, half width r
+                if (y >= 0 && y < s.H) {
+                    const int xlo = max(0, s.sx - r), xhi = min(s.W - 1, s.sx + r);
+                    gather(s, y, s.iw0 - RWD / 2 + wl, xlo, xhi, fg, bg);
+                    if (wl == 0) gather(s, y, s.iw0 + RWD / 2, xlo, xhi, fg, bg);
+                }
             }
-        }
-        if (r + 1 <= RW) {
-            const int y = s.sy + r + 1;                        // lower half, half width RW-r-1
-            if (y >= 0 && y < s.H) {
-                const int hw = RW - r - 1;
-                const int xlo = max(0, s.sx - hw), xhi = min(s.W - 1, s.sx + hw);
-                gather(s, y, s.iw0 + (lane < 16 ? lane : lane - 32), xlo, xhi, fg, bg);
-                if (lane == 16) gather(s, y, s.iw0 + 16, xlo, xhi, fg, bg);
+            if (r + 1 <= RW) {
+                const int y = s.sy + r + 1;                        // lower half, half width RW-r-1
+                if (y >= 0 && y < s.H) {
+                    const int hw = RW - r - 1;
+                    const int xlo = max(0, s.sx - hw), xhi = min(s.W - 1, s.sx + hw);
+                    gather(s, y, s.iw0 + (wl < RWD / 2 ? wl : wl - RWD), xlo, xhi, fg, bg);
+                    if (wl == RWD / 2) gather(s, y, s.iw0 + RWD / 2, xlo, xhi, fg, bg);
+                }
             }
+            const int pw = r * RWD + ((wl + r) & (RWD - 1));
+            OF[pw] = fg;
+            if (GEN) OB[pw] = bg;
         }
-        const int pw = (r << 5) | ((lane + r) & 31);
-        OF[pw] = fg;
-        if (GEN) OB[pw] = bg;
     }
 }
 
@@ -152,15 +172,17 @@ struct Ctl {
 };
 
 // a target cell was reached at level k with j mask pixels on the path: hop = k + j
+template <bool WIDE>
 __device__ __forceinline__ int probe_settle(const K2Params& p, const uint32_t* hash, const uint32_t* cand,
                                             const Chain& ch, uint32_t key, int k, int j) {
+    constexpr int ESH = Geo<WIDE>::ESH;
     int n = 0;
     uint32_t h = hash_slot(key);
     for (;;) {
         const uint32_t e = hash[h];
         if (e == kEmpty) break;
-        if ((e >> 13) == key) {
-            const uint32_t c = cand[e & 0x1FFFu];
+        if ((e >> ESH) == key) {
+            const uint32_t c = cand[e & ((1u << ESH) - 1u)];
             const long long o = ch.orow[c >> 30] + (long long)(c & 0x3FFFFFFFu);
             p.path_len[o] = k + j + 1;
             p.unreachable[o] = 0;
@@ -175,24 +197,28 @@ __device__ __forceinline__ int probe_settle(const K2Params& p, const uint32_t* h
 // One work item = one source of a chain leader, processed by the whole CTA.  Returns true when
 // the item must be redone by the general kernel (fast kernel only).  All control flow is
 // CTA-uniform (decisions are read from shared memory after a barrier).
-template <bool GEN, int NT>
+template <bool GEN, int NT, bool WIDE>
 __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
+    using G = Geo<WIDE>;
+    constexpr int kCal = G::CAL;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const uint32_t lt = lanemask_lt();
     const int RW = p.max_px;
-    const int nwords = (RW + 1) * kRowWords;
+    const int nwords = (RW + 1) * G::RWD;
     constexpr int QCAP = kGenQCap;
-    constexpr int GQCAP = kGCap;
+    constexpr int GQCAP = G::GQ;
 
-    uint32_t* const OF = smem;
-    uint32_t* const OB = OF + (GEN ? nwords : 0);
-    uint32_t* const q0 = OB + nwords;
-    uint32_t* const hash = q0 + 2 * QCAP;
-    int* const cal0 = (int*)(hash + kHashSize);          // general only: [2][kSeedCal]
+    // global scratch: candidates | frontier overflow [2][GQCAP] | seed lists [2][GQCAP] | (WIDE) both bitmaps
     uint32_t* const cand = gscr;
     uint32_t* const gq0 = gscr + kCandCap;
     uint32_t* const gs0 = gq0 + 2 * (size_t)GQCAP;       // general only: [2][GQCAP]
+    // shared memory: (not WIDE) both bitmaps | frontier [2][QCAP] | target hash | seed calendar [2][kCal]
+    uint32_t* const OF = WIDE ? gs0 + 2 * (size_t)GQCAP : smem;
+    uint32_t* const OB = OF + (GEN ? nwords : 0);
+    uint32_t* const q0 = WIDE ? smem : OB + nwords;
+    uint32_t* const hash = q0 + 2 * QCAP;
+    int* const cal0 = (int*)(hash + kHashSize);
     Chain& ch = ctl.ch;
 
     // ---- which chain / source -------------------------------------------------------------
@@ -233,7 +259,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
     const bool src_in = s.sy >= 0 && s.sy < p.H && s.sx >= 0 && s.sx < p.W;
     const long long r2 = (long long)RW * RW;
     const int o = s.o;
-    uint8_t* const par = p.trace_par ? p.trace_par + (size_t)blockIdx.x * kTraceParBytes : nullptr;
+    uint8_t* const par = p.trace_par ? p.trace_par + (size_t)blockIdx.x * G::PAR : nullptr;
 
     int tt = 0;                        // next target of the flattened chain target list
     for (;;) {                         // passes of <= kHashMaxLoad candidates (one on real data)
@@ -274,8 +300,8 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                 if (is_cand) {
                     const uint32_t slot = (uint32_t)base + __popc(bal & lt);
                     cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
-                    const uint32_t entry = ((uint32_t)fold_index(dy, dx + o, RW) << 13) | slot;
-                    uint32_t h = hash_slot(entry >> 13);
+                    const uint32_t entry = ((uint32_t)fold_index<WIDE>(dy, dx + o, RW) << G::ESH) | slot;
+                    uint32_t h = hash_slot(entry >> G::ESH);
                     while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (kHashSize - 1);
                 }
             }
@@ -283,20 +309,20 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
         }
         const int ncand = ctl.ncand;
         if (ncand > 0) {
-            stage_window<GEN, NT>(s, OF, OB);
+            stage_window<GEN, NT, WIDE>(s, OF, OB);
             __syncthreads();
             if (tid == 0) {            // close the source cell, seed the search with it
-                const int c = fold_index(0, o, RW);
-                OF[phys_word(c)] &= ~(1u << (c & 31));
-                if (GEN) OB[phys_word(c)] &= ~(1u << (c & 31));
-                q0[0] = pack_cell(0, o);
-                if (GEN) gs0[0] = pack_cell(0, o);
+                const int c = fold_index<WIDE>(0, o, RW);
+                OF[phys_word<WIDE>(c)] &= ~(1u << (c & 31));
+                if (GEN) OB[phys_word<WIDE>(c)] &= ~(1u << (c & 31));
+                q0[0] = pack_cell<WIDE>(0, o);
+                if (GEN) gs0[0] = pack_cell<WIDE>(0, o);
                 ctl.cnt[0] = GEN ? 0 : 1; ctl.cnt[1] = 0; ctl.cnt[2] = 0;
                 ctl.settled[0] = 0; ctl.settled[1] = 0; ctl.settled[2] = 0;
                 ctl.unsettled = ncand;
                 ctl.seedcnt = 0;
             }
-            if (GEN) for (int jj = tid; jj < kSeedCal; jj += NT) cal0[jj] = 1;    // the source: one seed tagged j = 0
+            if (GEN) for (int jj = tid; jj < kCal; jj += NT) cal0[jj] = 1;    // the source: one seed tagged j = 0
             __threadfence_block();
             __syncthreads();
 
@@ -313,8 +339,8 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                 for (int k = 0; k <= RW && n_seeds > 0 && unsettled > 0; ++k) {
                     const uint32_t* const gs_cur = gs0 + (size_t)(k & 1) * GQCAP;
                     uint32_t* const gs_nxt = gs0 + (size_t)((k + 1) & 1) * GQCAP;
-                    const int* const cal_cur = cal0 + (k & 1) * kSeedCal;      // #seeds tagged <= j
-                    int* const cal_nxt = cal0 + ((k + 1) & 1) * kSeedCal;
+                    const int* const cal_cur = cal0 + (k & 1) * kCal;          // #seeds tagged <= j
+                    int* const cal_nxt = cal0 + ((k + 1) & 1) * kCal;
                     int j = 0;
                     while (cal_cur[j] == 0) ++j;                      // first seeded j of this level
                     const int jstart = j;
@@ -348,17 +374,19 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                                 bool seed = false;
                                 if (i < nlist) e = i < QCAP ? qcur[i] : gcur[i - QCAP];
                                 else { e = gs_cur[sp + (i - nlist)]; seed = true; }
-                                const int dy = (int)(e >> 11) - 512, cx = (int)(e & 2047u) - 512;
+                                const int dy = (int)(e >> G::CSH) - G::HALF, cx = (int)(e & ((1u << G::CSH) - 1u)) - G::HALF;
                                 // off-mask cells settle when their level starts consuming them: by then no
                                 // lower level has reached hop max_px
                                 if (seed && k > 0 && dir == 0)
-                                    my_set += probe_settle(p, hash, cand, ch, (uint32_t)fold_index(dy, cx, RW), k, j);
-                                idx = fold_index(dy + ddy, cx + dcx, RW);
-                                ne = pack_cell(dy + ddy, cx + dcx);
-                                const int pw = phys_word(idx);
+                                    my_set += probe_settle<WIDE>(p, hash, cand, ch, (uint32_t)fold_index<WIDE>(dy, cx, RW), k, j);
+                                idx = fold_index<WIDE>(dy + ddy, cx + dcx, RW);
+                                ne = pack_cell<WIDE>(dy + ddy, cx + dcx);
+                                const int pw = phys_word<WIDE>(idx);
                                 const uint32_t bit = 1u << (idx & 31);
-                                if (OF[pw] & bit) got_fg = (atomicAnd(&OF[pw], ~bit) & bit) != 0;
-                                else if (OB[pw] & bit) got_bg = (atomicAnd(&OB[pw], ~bit) & bit) != 0;
+                                // (WIDE: the bitmaps are global memory changed by atomics: read around L1)
+                                const uint32_t wf = WIDE ? __ldcg(&OF[pw]) : OF[pw];
+                                if (wf & bit) got_fg = (atomicAnd(&OF[pw], ~bit) & bit) != 0;
+                                else if ((WIDE ? __ldcg(&OB[pw]) : OB[pw]) & bit) got_bg = (atomicAnd(&OB[pw], ~bit) & bit) != 0;
                                 if (par && (got_fg || got_bg)) par[idx] = (uint8_t)dir;   // entered from (dy, cx)
                             }
                             const uint32_t bf = __ballot_sync(kFull, got_fg);
@@ -370,7 +398,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                                 if (got_fg) {
                                     const int slot = pos + __popc(bf & lt);
                                     if (slot < QCAP) qnxt[slot] = ne; else gnxt[slot - QCAP] = ne;
-                                    if (k + j + 1 < RW) my_set += probe_settle(p, hash, cand, ch, (uint32_t)idx, k, j + 1);
+                                    if (k + j + 1 < RW) my_set += probe_settle<WIDE>(p, hash, cand, ch, (uint32_t)idx, k, j + 1);
                                 }
                             }
                             if (bb) {
@@ -393,7 +421,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                     // ---- level end: complete the next level's calendar ------------------------------
                     __syncthreads();
                     const int total_next = ctl.seedcnt;
-                    for (int jj = tid; jj < kSeedCal; jj += NT) {
+                    for (int jj = tid; jj < kCal; jj += NT) {
                         if (jj >= j) cal_nxt[jj] = total_next;
                         else if (jj < jstart) cal_nxt[jj] = 0;
                     }
@@ -412,10 +440,9 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
 
 }  // namespace
 
-__global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Params p) {
-    extern __shared__ __align__(16) uint32_t smem[];
-    __shared__ Ctl ctl;
-    uint32_t* const gscr = p.gen_scratch + (size_t)blockIdx.x * kGenScratchWords;
+template <bool WIDE>
+__device__ __forceinline__ void general_body(const K2Params& p, uint32_t* smem, Ctl& ctl) {
+    uint32_t* const gscr = p.gen_scratch + (size_t)blockIdx.x * Geo<WIDE>::SCRATCH;
     const int total = p.counters[1];
     for (;;) {
         __syncthreads();
@@ -424,21 +451,21 @@ __global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Param
         const int t = ctl.item;
         if (t >= total) break;
         const int item = p.gen_list[t];
-        run_item<true, kK2Threads>(p, item, smem, gscr, ctl);
+        run_item<true, kK2Threads, WIDE>(p, item, smem, gscr, ctl);
         if (p.trace_par) {             // one (source, target) request per pair: walk the entry directions back
             __syncthreads();
             if (threadIdx.x == 0) {
                 const axb_pair_desc pd = p.pairs[item];
                 const int sy = p.dets_yx[2 * (size_t)pd.src_off], sx = p.dets_yx[2 * (size_t)pd.src_off + 1];
                 const int ty = p.dets_yx[2 * (size_t)pd.dst_off], tx = p.dets_yx[2 * (size_t)pd.dst_off + 1];
-                const uint8_t* const par = p.trace_par + (size_t)blockIdx.x * kTraceParBytes;
+                const uint8_t* const par = p.trace_par + (size_t)blockIdx.x * Geo<WIDE>::PAR;
                 int32_t* const out = p.trace_yx + (size_t)item * p.max_px * 2;
                 int L = p.unreachable[pd.out_off] ? 0 : p.path_len[pd.out_off];
                 const int x0 = sx & ~31, o = sx & 31;
                 int dy = ty - sy, cx = tx - x0;
                 for (int n = L - 1; n >= 1; --n) {
                     out[2 * n] = sy + dy; out[2 * n + 1] = x0 + cx;
-                    const int d = par[fold_index(dy, cx, p.max_px)] & 3;
+                    const int d = par[fold_index<WIDE>(dy, cx, p.max_px)] & 3;
                     dy -= d == 0 ? -1 : d == 3 ? 1 : 0;
                     cx -= d == 1 ? -1 : d == 2 ? 1 : 0;
                 }
@@ -451,6 +478,28 @@ __global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Param
         }
     }
 }
+
+__global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Params p) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ Ctl ctl;
+    general_body<false>(p, smem, ctl);
+}
+
+// 512 <= max_px <= 1023: every source goes through this kernel (bitmaps in global scratch)
+__global__ void __launch_bounds__(kK2Threads, 1) k2_general_wide_kernel(const K2Params p) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ Ctl ctl;
+    general_body<true>(p, smem, ctl);
+}
+
+// gen_list = every work item (max_px beyond the tile-word kernels' window)
+__global__ void __launch_bounds__(256) k2_all_to_general_kernel(const int* __restrict__ work_prefix, int n_pairs,
+                                                                int* __restrict__ gen_list, int* __restrict__ counters) {
+    const int total = work_prefix[n_pairs];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) gen_list[i] = i;
+    if (blockIdx.x == 0 && threadIdx.x == 0) counters[1] = total;
+}
+
 // Chains + prefix sums + counter reset, one CTA.
 //   same key = same (mask_idx, src_off, n_src): the searches of the two pairs are identical, only
 //   the targets differ.  prev/next link same-key pairs inside a +-kChainWindow index window; a
@@ -528,11 +577,19 @@ void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, i
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {
+    if (p.max_px > kFastMaxPx) {
+        k2_general_wide_kernel<<<grid, kK2Threads, k2_gen_wide_smem_bytes(), stream>>>(p);
+        return;
+    }
     static unsigned long long attr_set = 0ull;
     if (first_use_on_device(attr_set)) {
-        cudaFuncSetAttribute(k2_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_gen_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_gen_smem_bytes(kFastMaxPx));
     }
     k2_general_kernel<<<grid, kK2Threads, k2_gen_smem_bytes(p.max_px), stream>>>(p);
+}
+
+void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream) {
+    k2_all_to_general_kernel<<<148, 256, 0, stream>>>(work_prefix, n_pairs, gen_list, counters);
 }
 
 }  // namespace axb

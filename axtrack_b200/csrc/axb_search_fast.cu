@@ -87,30 +87,6 @@ struct Win {
     int RW, NR, oy, ox;
 };
 
-// Where tile (tile row tr, tile column tc of the window) lives in the tiled mask and which of its
-// pixels lie inside the diamond; nullptr when none does.  hw_in / hw_out: half widths of the
-// narrowest / widest image row of the tile row.
-__device__ __forceinline__ const uint32_t* window_tile(const Win& w, int tr, int tc, int hw_in, int hw_out, uint32_t& m) {
-    const int x0 = 8 * tc - w.ox;                       // dx of the tile's first pixel
-    m = 0u;
-    if (x0 + 7 < -hw_out || x0 > hw_out) return nullptr;
-    const int ty = w.ty0 + tr, tx = w.tx0 + tc;
-    if (ty < 0 || ty >= w.TH || tx < 0 || tx >= w.TWp) return nullptr;
-    m = 0xFFFFFFFFu;
-    if (x0 < -hw_in || x0 + 7 > hw_in) {                // the diamond edge crosses the tile
-        m = 0u;
-        const int dy0 = 4 * tr - w.oy;
-        #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int hw = w.RW - abs(dy0 + r);
-            const int lo = max(-hw - x0, 0), hi = min(hw - x0, 7);
-            if (hw >= 0 && lo <= hi) m |= (((0xFFu >> (7 - hi)) & (0xFFu << lo)) & 0xFFu) << (8 * r);
-        }
-        if (m == 0u) return nullptr;
-    }
-    return w.tiles + (size_t)ty * w.TWp + tx;
-}
-
 // Four adjacent tiles (a 16-byte aligned quad: 32 x 4 pixels) of window tile row tr starting at
 // tile column tcq (a multiple of 4): where they live in the tiled mask, or nullptr when no pixel
 // of the quad lies inside the diamond or the image.  x0 = dx of the quad's first pixel.
@@ -680,7 +656,7 @@ void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream) {
     static unsigned long long attr_set = 0ull;
     if (first_use_on_device(attr_set)) {
-        cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_fast_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_fast_smem_bytes(kFastMaxPx));
         cudaFuncSetAttribute(k2_fast_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     }
     k2_fast_kernel<<<grid, kFastThreads, k2_fast_smem_bytes(p.max_px), stream>>>(p);

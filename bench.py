@@ -330,7 +330,11 @@ def run_b200(args, wl):
             traffic = json.load(open(tf)).get(args.workload)
         except Exception:
             traffic = None
-    roofline = dict(bound='hbm', kernel='K2 launch group = k2_sparse_kernel (dominant, ~90 % by the ncu launch list) + tile/prep/dense/general; one launch = all frame pairs of the block',
+    if MAX_PX != 500:
+        traffic = None            # the committed ncu capture is of the max_px = 500 run
+    klabel = ('K2 launch group = k2_sparse_kernel (dominant, ~90 % by the ncu launch list) + tile/prep/dense/general; one launch = all frame pairs of the block'
+              if MAX_PX <= 511 else 'K2 launch group = prep + k2_general_wide_kernel (max_px > 511: every source on the all-levels kernel, window bitmaps in global scratch)')
+    roofline = dict(bound='hbm', kernel=klabel,
                     achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
                     peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
                     algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)),
@@ -449,6 +453,7 @@ def run_c5(args):
 
 
 def main():
+    global MAX_PX
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
@@ -457,7 +462,10 @@ def main():
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c5'])
     ap.add_argument('--cpu-calls', type=int, default=1200, help='in-range A* calls of the cpu_baseline sample (~15 ms each at 2048^2)')
     ap.add_argument('--ref-calls', type=int, default=250, help='in-range A* calls per --impl reference step')
+    ap.add_argument('--max-px', type=int, default=500,
+                    help='max_px_assoc_dist (SURVEY 8d: configs[2] is also swept at 1000; > 511 runs the wide all-levels kernel)')
     args = ap.parse_args()
+    MAX_PX = args.max_px
     if args.workload == 'c5':
         return run_c5(args)
     wl = WORKLOADS[args.workload]

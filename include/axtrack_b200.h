@@ -36,8 +36,10 @@ extern "C" {
 #define AXB_ERR_UNSUPPORTED_WEIGHT -7 /* weight grid holds values other than {1, 65536}        */
 
 /* Largest max_px (the reference's max_px_assoc_dist / max_path_length; 500 in
- * AxonDetections.py:77) the shared-memory search window supports. */
-#define AXB_MAX_PX 511
+ * AxonDetections.py:77, an attribute the reference honours at :623-625,736).  Up to 511 the
+ * search window lives in shared memory (tile-word kernels); 512..1023 run on the all-levels
+ * kernel with its window bitmaps in global memory (several times slower per source). */
+#define AXB_MAX_PX 1023
 
 typedef struct axb_ctx axb_ctx;
 

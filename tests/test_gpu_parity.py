@@ -109,7 +109,7 @@ def test_cost_matrix_vs_oracle_random(cuda, seed):
         for _ in range(int(rng.integers(0, 8))):
             y, x, g = int(rng.integers(0, H)), int(rng.integers(0, W)), int(rng.integers(1, 5))
             m[y:y + g, x:x + g] = False
-        max_px = int(rng.choice([1, 2, 12, 25, 40, 80, 150, 500, 511]))
+        max_px = int(rng.choice([1, 2, 12, 25, 40, 80, 150, 500, 511, 512, 1023]))
         fg = np.argwhere(m)
 
         def pick(n):
@@ -369,6 +369,38 @@ def test_window_rim_at_largest_radii(cuda):
                 dst = np.array(dst, np.int32)
                 _check(_gpu_cost(cuda, mask, src, dst, max_px), oracle.cost_matrix_rule(mask, src, dst, max_px),
                        (field, max_px, sy, sx))
+
+
+@pytest.mark.gpu
+def test_wide_radius(cuda):
+    """max_px_assoc_dist is an attribute the reference honours at any value (AxonDetections.py:623-625,
+    736; SURVEY 8d sweeps {500, 1000}): 512 <= max_px <= 1023 runs every source on the wide
+    all-levels kernel (2048-bit folded rows, bitmaps in global scratch).  Corridor mask with sources
+    on and off it, an open field with targets on the rim, and a frame smaller than the window."""
+    rng = np.random.default_rng(21)
+    H, W = 1500, 1700
+    mask = synth.make_mask(H, W, seed=9, pitch=(90, 200), width=(6, 16))
+    fg = np.argwhere(mask)
+    src = fg[rng.integers(0, len(fg), 5)].astype(np.int32)
+    src = np.concatenate([src, np.array([[3, 4], [H - 1, W - 1], [700, 811]], np.int32)])
+    dst = np.concatenate([fg[rng.integers(0, len(fg), 700)], np.stack([rng.integers(0, H, 40), rng.integers(0, W, 40)], 1)]).astype(np.int32)
+    for max_px in (512, 777, 1000, 1023):
+        _check(_gpu_cost(cuda, mask, src, dst, max_px), oracle.cost_matrix_rule(mask, src, dst, max_px), ('corridors', max_px))
+    ones = np.ones((2100, 2100), np.uint8)
+    for max_px, (sy, sx) in ((1023, (1040, 1051)), (1000, (1030, 1040))):
+        dst = []
+        for y in range(sy - max_px, sy + max_px + 1, 37):
+            hw = max_px - abs(y - sy)
+            for side in (-1, 1):
+                for inward in (0, 1, 2, 9):
+                    if hw - inward >= 0:
+                        dst.append((y, sx + side * (hw - inward)))
+        dst = np.array(dst, np.int32)
+        src = np.array([[sy, sx]], np.int32)
+        _check(_gpu_cost(cuda, ones, src, dst, max_px), oracle.cost_matrix_rule(ones, src, dst, max_px), ('rim', max_px))
+    small = (rng.random((90, 130)) < 0.7).astype(np.uint8)
+    pts = np.stack([rng.integers(0, 90, 30), rng.integers(0, 130, 30)], 1).astype(np.int32)
+    _check(_gpu_cost(cuda, small, pts[:10], pts, 900), oracle.cost_matrix_rule(small, pts[:10], pts, 900), 'small frame')
 
 
 @pytest.mark.gpu

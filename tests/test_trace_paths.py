@@ -49,6 +49,16 @@ def test_paths_on_corridor_mask():
     assert _check_paths(mask, src, dst, 500) > 20
 
 
+def test_paths_wide_radius():
+    """max_px beyond 511: the wide all-levels kernel records and walks back the entry directions."""
+    rng = np.random.default_rng(6)
+    mask = synth.make_mask(1300, 1400, seed=4, pitch=(80, 170), width=(6, 14))
+    fg = np.argwhere(mask)
+    src = fg[rng.integers(0, len(fg), 4)].astype(np.int32)
+    dst = fg[rng.integers(0, len(fg), 30)].astype(np.int32)
+    assert _check_paths(mask, src, dst, 900) > 20
+
+
 def test_paths_through_background_and_short_cutoffs():
     """Sources / targets off the mask (paths that pay 65536 per background pixel), gaps, small max_px."""
     rng = np.random.default_rng(9)
