@@ -175,7 +175,7 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     if (rc != AXB_OK) return rc;
     const bool wide = max_px > axb::kFastMaxPx;
     if (wide && !c->k2_wide_scratch)
-        AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kGenScratchWordsWide * sizeof(uint32_t)));
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kWideCtasPerSm * axb::kGenScratchWordsWide * sizeof(uint32_t)));
     if (!wide) axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
     int* const work_prefix = c->prefix_dev;
     int* const all_prefix = c->prefix_dev + c->prefix_cap;
@@ -193,7 +193,7 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
     if (wide) {      // beyond the tile-word kernels' window: every source goes through the wide all-levels kernel
         axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
-        axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
+        axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * axb::kWideCtasPerSm, total_src)), s);
         c->launches += 3;
         AXB_CUDA(c, cudaGetLastError());
         return AXB_OK;
@@ -389,9 +389,9 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     if (rc != AXB_OK) return rc;
     const bool wide = max_px > axb::kFastMaxPx;
     if (!wide && !c->trace_par) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par, (size_t)c->k2_gen_ctas * axb::kTraceParBytes));
-    if (wide && !c->trace_par_wide) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par_wide, (size_t)c->k2_gen_ctas * axb::kTraceParBytesWide));
+    if (wide && !c->trace_par_wide) AXB_CUDA(c, cudaMalloc((void**)&c->trace_par_wide, (size_t)c->k2_gen_ctas * axb::kWideCtasPerSm * axb::kTraceParBytesWide));
     if (wide && !c->k2_wide_scratch)
-        AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kGenScratchWordsWide * sizeof(uint32_t)));
+        AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kWideCtasPerSm * axb::kGenScratchWordsWide * sizeof(uint32_t)));
     // one 1 x 1 frame pair per request: detections rows 2i (source), 2i+1 (target)
     std::vector<int32_t> dets((size_t)n_req * 4);
     std::vector<axb_pair_desc> pairs((size_t)n_req);
@@ -429,7 +429,7 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = wide ? c->k2_wide_scratch : c->k2_gen_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
     p.trace_par = wide ? c->trace_par_wide : c->trace_par; p.trace_yx = path_yx_dev; p.trace_len = path_len_dev;
-    axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, n_req)), s);
+    axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * (wide ? axb::kWideCtasPerSm : 1), n_req)), s);
     c->launches += 2;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;

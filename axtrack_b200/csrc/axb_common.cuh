@@ -43,6 +43,7 @@ constexpr int kSparseCtasPerSm = 10;
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
 constexpr int kGCapWide = 1 << 21;
+constexpr int kWideCtasPerSm = 4;     // wide all-levels kernel: bound by the latency of L2 atomics, 28 KB of shared memory
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;
 
 struct K2Params {

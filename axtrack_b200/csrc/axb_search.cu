@@ -486,7 +486,7 @@ __global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Param
 }
 
 // 512 <= max_px <= 1023: every source goes through this kernel (bitmaps in global scratch)
-__global__ void __launch_bounds__(kK2Threads, 1) k2_general_wide_kernel(const K2Params p) {
+__global__ void __launch_bounds__(kK2Threads, kWideCtasPerSm) k2_general_wide_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     general_body<true>(p, smem, ctl);
