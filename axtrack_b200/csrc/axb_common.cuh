@@ -28,12 +28,12 @@ constexpr int kSeedCalWide = 1024;
 constexpr int kFastMaxPx = 511;       // largest radius of the 1024-column folded window (tile-word kernels, shared-memory bitmaps)
 static_assert(AXB_MAX_PX == 1023, "wide layout: 2048-bit folded rows");
 // fast kernel (level 0 only): 3 CTAs per SM
-constexpr int kFastThreads = 96;     // fast kernels: one CTA (4 warps) per source search, one thread per frontier entry
+constexpr int kFastThreads = 96;      // fast kernels: one CTA (3 warps) per source search, one thread per frontier entry
 constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entries per buffer
 // dense window (every tile word of the folded diamond, 64.5 KB): 3 CTAs per SM
 constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory
 constexpr int kFastCtasPerSm = 3;
-// sparse window (only the non-zero tile words + a presence/base table): 8 CTAs per SM
+// sparse window (only the non-zero tile words + a presence/base table): 10 CTAs per SM
 constexpr int kSparseWords = 3936;    // non-zero tile words a sparse window can hold (15.4 KB)
 constexpr int kSparseQCap = 144;
 constexpr int kSparseHash = 512;

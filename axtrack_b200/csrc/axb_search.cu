@@ -20,25 +20,19 @@
 // path_length = k + j + 1 if that is <= max_px.
 //
 // Mapping to the SM.  A search is ~max_px dependent wavefronts of a few hundred cells: latency
-// bound.  One CTA of kK2Threads (8 warps) per source, one __syncthreads per wavefront, and
-// throughput from 3 resident CTAs per SM x 148 SMs of independent searches.
-//   k2_fast_kernel     level 0 only (the answer for every source whose mask component reaches
-//                      hop max_px or contains all its in-range targets -- nearly all of them on
-//                      real data).  Window = one 64 KB "open mask pixel" bitmap in shared memory
-//                      in the folded-diamond layout of axb_common.cuh (rows rotated by their index
-//                      so that a vertical run of cells spreads over the 32 banks), staged with
-//                      aligned 128 B row reads of the bit-packed mask; claiming a cell is one
-//                      shared-memory atomicAnd by one lane per (frontier cell, direction); the
-//                      frontier queue (shared, global overflow) is appended with one
-//                      warp-aggregated atomicAdd per 32 lanes; targets are
-//                      found through a 4 KB shared hash of their window cells probed by the lane
-//                      that claims a cell.  75 KB per CTA -> 3 CTAs per SM, persistent over a
-//                      ticket counter.
-//   k2_general_kernel  all levels (second bitmap "open off-mask pixel", per-level seed lists in
-//                      global memory with a per-j calendar in shared memory) for the sources the
-//                      fast kernel defers: level 0 exhausted below hop max_px with targets still
-//                      open (source off the mask or in a small component).
-//   k2_prep_kernel     chains, work prefix sums, counter reset (one CTA, tiny).
+// bound.  The level-0 searches (nearly all sources on real data) run on the tile-word kernels of
+// axb_search_fast.cu; this file holds
+//   k2_general_kernel       all levels, one CTA of kK2Threads (8 warps) per source, one lane per
+//                           (frontier cell, direction): per-cell bitmaps "open mask pixel" and
+//                           "open off-mask pixel" in shared memory (folded-diamond layout of
+//                           axb_common.cuh, rows rotated by their index over the 32 banks),
+//                           per-level seed lists in global memory with a per-j calendar in shared
+//                           memory; for the sources the fast kernels defer (level 0 exhausted
+//                           below hop max_px with targets still open: source off the mask or in
+//                           a small component) and for path tracing (K4).
+//   k2_general_wide_kernel  the same search for 512 <= max_px <= 1023: 2048-bit folded rows,
+//                           bitmaps in the CTA's global scratch, every source.
+//   k2_prep_kernel          chains, work prefix sums, counter reset (one CTA, tiny).
 #include "axb_common.cuh"
 
 namespace axb {

@@ -12,8 +12,10 @@
 // pixels to (sx & ~31), and the diamond is FOLDED on a circle of 128 tile columns: tile rows
 // tr <= 0 live in folded row tr+NR-1 with the source's aligned column at tile column 64, tile
 // rows tr >= 1 in folded row tr-1 with it at tile column 0; NR = ceil(RW/4)+1.  The half widths of
-// the two tile rows sharing a folded row add up to <= RW-1, so their pixels never meet on the
-// 1024 px circle.  Only in-diamond mask pixels are staged as open and cells at hop RW are never
+// the two tile rows sharing a folded row add up to <= 2*RW - 4*NR + 3 <= 509, so their pixels
+// never meet on the 1024 px circle (above RW = 504 they can share a tile WORD, and a row can wrap
+// onto its own first tile: stage_window ORs the disjoint pixels of all candidate tiles).
+// Only in-diamond mask pixels are staged as open and cells at hop RW are never
 // expanded, so every candidate bit of an expansion is a true 4-neighbour: no bound checks.
 //   key of a tile word = half << 15 | folded row << 7 | tile column.
 //
@@ -24,9 +26,11 @@
 //
 // Two instantiations of the same search:
 //   k2_sparse_kernel  window = only the NON-ZERO tile words (<= kSparseWords) + a (presence
-//                     bits, base index) pair per 32 tile columns: ~28 KB per search -> 8 CTAs
-//                     per SM.  A search is ~max_px dependent wavefronts (latency bound), so the
-//                     throughput comes from the number of resident searches.
+//                     bits, base index | target flags) pair per 32 tile columns, target hash
+//                     in the CTA's global scratch: 21 KB and 3 warps per search -> 10 CTAs per
+//                     SM.  A search is ~max_px dependent wavefronts (latency bound), so the
+//                     throughput comes from the number of resident searches.  A launch too
+//                     small to fill the slots gets larger windows instead (launch_k2_sparse).
 //   k2_fast_kernel    dense window (64.5 KB, 3 CTAs per SM) for the sources whose window has
 //                     more non-zero tile words than the sparse layout holds (dense masks).
 #include "axb_common.cuh"
