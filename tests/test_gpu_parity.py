@@ -324,6 +324,9 @@ def test_sparse_window_multi_pass_and_dense_fallback(cuda):
     src = fg[rng.integers(0, len(fg), 6)].astype(np.int32)
     dst = fg[rng.integers(0, len(fg), 2500)].astype(np.int32)
     _check(_gpu_cost(cuda, mask, src, dst, 500), oracle.cost_matrix_rule(mask, src, dst, 500), 'sparse multi-pass')
+    # the same with enough sources to fill the CTA slots (small windows, target hash in global scratch)
+    src = fg[rng.integers(0, len(fg), 800)].astype(np.int32)
+    _check(_gpu_cost(cuda, mask, src, dst[:1200], 500), oracle.cost_matrix_rule(mask, src, dst[:1200], 500), 'sparse multi-pass, full launch')
     ones = np.ones((H, W), np.uint8)
     ones[300:800, 600] = 0
     src = np.array([[550, 560], [10, 10], [1099, 1199], [550, 640]], np.int32)
