@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libaxtrack_b200.so')
+# AXTRACK_B200_LIB: another build of the same library (csrc/Makefile `check` / `timing`), for debugging only
+LIB_PATH = os.environ.get('AXTRACK_B200_LIB') or os.path.join(_HERE, 'libaxtrack_b200.so')
 
 OK = 0
 ERR_CUDA = -1

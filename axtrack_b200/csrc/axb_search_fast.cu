@@ -34,6 +34,13 @@
 //   k2_fast_kernel    dense window (64.5 KB, 3 CTAs per SM) for the sources whose window has
 //                     more non-zero tile words than the sparse layout holds (dense masks).
 #include "axb_common.cuh"
+#ifdef AXB_CHECK       // `make check`: index asserts in the search kernels (compute-sanitizer stand-in), never shipped
+#undef NDEBUG
+#include <cassert>
+#define AXB_ASSERT(c) assert(c)
+#else
+#define AXB_ASSERT(c) do { } while (0)
+#endif
 
 namespace axb {
 
@@ -412,9 +419,11 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 base = __shfl_sync(kFull, base, 0);
                 if (is_cand) {
                     const uint32_t slot = (uint32_t)base + __popc(bal & lt);
+                    AXB_ASSERT(slot < (uint32_t)kCandCap && slot < 2048u);
                     cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
                     int bit;
                     const uint32_t key = cell_key(dy, dx, w.oy, w.ox, NR, bit);
+                    AXB_ASSERT(((key & 0x7FFFu) >> 7) < (uint32_t)NR && bit >= 0 && bit < 32);
                     const uint32_t entry = (key << 16) | ((uint32_t)bit << 11) | slot;
                     uint32_t h = hash_slot<HASH>(key);
                     while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (HASH - 1);
@@ -448,6 +457,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     there = (pb.x >> (widx & 31)) & 1u;
                     widx = (int)(pb.y & 0xFFFFu) + __popc(pb.x & ((1u << (widx & 31)) - 1u));
                 }
+                AXB_ASSERT(!there || widx < (SPARSE ? p.sparse_words : NR * kTC));
                 if (there) WIN[widx] &= ~(1u << bit);
                 q0[0] = make_uint2(1u << bit, key);
                 ctl.wc[0][0] = 1; ctl.wc[0][1] = 0; ctl.wc[0][2] = 0; ctl.wc[0][3] = 0;
@@ -467,10 +477,12 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             auto resolve = [&](uint32_t key, uint32_t& want, uint32_t& aux) -> uint32_t {
                 const uint32_t widx = key & 0x7FFFu;
                 if (!SPARSE) return win_s + 4u * widx;
+                AXB_ASSERT(!want || (widx >> 7) < (uint32_t)NR);
                 const uint2 pb = lds64_if(pb_s + 8u * (widx >> 5), want);
                 const uint32_t bit = 1u << (widx & 31u);
                 if (!(pb.x & bit)) want = 0u;
                 aux = pb.y;
+                AXB_ASSERT(!want || (pb.y & 0xFFFFu) + (uint32_t)__popc(pb.x & (bit - 1u)) < (uint32_t)p.sparse_words);
                 return win_s + 4u * ((pb.y & 0xFFFFu) + (uint32_t)__popc(pb.x & (bit - 1u)));
             };
             int unsettled = ncand;     // CTA-uniform: updated from ctl.wc[] after each barrier
@@ -496,6 +508,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const int sg = (i >= p1) + (i >= p2) + (i >= p3);
                     const int off = i - (sg == 0 ? 0 : sg == 1 ? p1 : sg == 2 ? p2 : p3);
                     const bool act = i < total;
+                    AXB_ASSERT(!act || (sg < kNW && off >= 0 && off < C::kSeg + kGSeg));
                     uint2 e = lds64_if(qcur_s + 8u * (uint32_t)(sg * C::kSeg + off), act && off < C::kSeg);
                     if (__any_sync(kFull, act && off >= C::kSeg)) {           // entries that spilled to global memory
                         if (act && off >= C::kSeg)
@@ -521,6 +534,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const uint32_t a3 = resolve(k3, cd3, auxn), a4 = resolve(k4, cd4, auxn);
                     // may the word hold a target?  sparse: flag of its column pair; dense: its hash slot is in use
                     bool maybe;
+                    AXB_ASSERT(!act || f != 0u);
                     if (SPARSE) maybe = f != 0u && ((aux0 >> (16u + ((k0 & 31u) >> 1))) & 1u);
                     else maybe = f != 0u && lds_if(hash_s + 4u * hash_slot<HASH>(k0), f) != kEmpty;
                     const uint32_t o0 = lds_if(a0, cd0) & cd0;
@@ -546,6 +560,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const int tot = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4);
                     if (tot) {
                         int slot = wn + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
+                        AXB_ASSERT(slot >= 0 && (wn + tot > C::kSeg + kGSeg || slot + (c0 != 0u) + (c1 != 0u) + (c2 != 0u) + (c3 != 0u) + (c4c != 0u) <= wn + tot));
                         if (wn + tot <= C::kSeg) {
                             uint32_t sa = qnxt_s + 8u * (uint32_t)slot;
                             sts64_if(sa, c0, k0, c0);   sa += c0 ? 8u : 0u;
