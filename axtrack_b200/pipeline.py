@@ -78,11 +78,12 @@ class Association:
 
 def associate_frames(Y, tile_yx, mask, max_px=500, max_num_misses=1, tilesize=512, conf_thr=0.55,
                      nms_dist=23, cap=None, mask_of_frame=None, want_cost=True, want_pre=False,
-                     mask_bits=None, t0=0):
+                     mask_bits=None, t0=0, out_alloc=None):
     """Y float32 CUDA [T, ntiles, Sx, Sy, 3]; tile_yx int32 CUDA [ntiles, 2]; mask uint8/bool CUDA
     [H, W] (static, the reference stacks one 2-D mask: Timelapse.py:213-214) or [n_masks, H, W] with
     ``mask_of_frame`` [T].  ``t0`` > 0: frames < t0 are halo frames (sources only), used by the
-    timepoint sharding.  Returns an ``Association``."""
+    timepoint sharding.  ``out_alloc(total, pairs)`` -> (path_len, unreachable, wcost|None) CUDA tensors
+    the kernels write into (sharding.PeerSlabs: rank 0's HBM over NVLink).  Returns an ``Association``."""
     ctx = ops.get_context(Y.device)
     l0 = ctx.launches
     det = ops.decode_nms(Y, tile_yx, tilesize, conf_thr, nms_dist, cap, want_pre=want_pre)
@@ -95,5 +96,6 @@ def associate_frames(Y, tile_yx, mask, max_px=500, max_num_misses=1, tilesize=51
     ops.raise_status(device=Y.device)
     keys = frame_pair_keys(T, max_num_misses, t0)
     pairs, total, _ = build_pairs(n_out, cap, keys, mask_of_frame)
-    pl, un, wc, _ = ops.cost_matrix_batch(mask_bits, W, det['yx'].view(-1, 2), pairs, max_px, want_cost)
+    out = out_alloc(total, pairs) if out_alloc is not None else None
+    pl, un, wc, _ = ops.cost_matrix_batch(mask_bits, W, det['yx'].view(-1, 2), pairs, max_px, want_cost, out=out)
     return Association(det, n_out, keys, pairs, pl, un, wc, ctx.launches - l0)

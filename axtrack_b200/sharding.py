@@ -63,6 +63,80 @@ def gather_to_rank0(path_len, unreachable, pair_shapes, group=None):
     return out
 
 
+class PeerSlabs:
+    """Gather without a payload transfer: rank 0's HBM holds one result slab per rank (symmetric
+    memory, peer-mapped over NVLink / NVSwitch) and every rank's K2 kernels store their path-length
+    and flag matrices straight into their slab, so the gather is the kernels' own epilogue.  A step
+    ends with one 16-byte all-reduce (which also orders rank 0's reads after every peer's stores)
+    instead of world-1 receives of tens of MB after the kernels.  CUDA + NCCL only.
+
+    Per step and rank: ``reserve`` (collective: grows the slabs when some rank needs more),
+    ``out_alloc`` (views for the kernels), ``publish`` (pair shapes + counts, then the all-reduce);
+    rank 0 then ``collect``s [(path_len, unreachable, pair_shapes)] per rank from its own memory."""
+
+    def __init__(self, device, group=None, cap_elems=1 << 20, cap_pairs=1024):
+        self.device, self.group = device, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.cap_elems = self.cap_pairs = 0
+        self._need = torch.zeros(2, dtype=torch.int64, device=device)
+        self._alloc(cap_elems, cap_pairs)
+
+    def _alloc(self, cap_elems, cap_pairs):
+        import torch.distributed._symmetric_memory as symm
+        al = lambda n: (int(n) + 255) & ~255
+        self.cap_elems, self.cap_pairs = int(cap_elems), int(cap_pairs)
+        self.o_un = al(4 * self.cap_elems)
+        self.o_shp = self.o_un + al(self.cap_elems)
+        self.o_meta = self.o_shp + al(16 * self.cap_pairs)
+        self.slab = self.o_meta + 256
+        nbytes = self.slab * self.world
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=self.device)      # rank 0's copy is the one in use
+        grp = self.group if self.group is not None else dist.group.WORLD
+        self.hdl = symm.rendezvous(self.buf, grp.group_name)
+        self.rank0 = self.buf if self.rank == 0 else self.hdl.get_buffer(0, (nbytes,), torch.uint8)
+
+    def _views(self, base, r):
+        s = base[r * self.slab:(r + 1) * self.slab]
+        return (s[:4 * self.cap_elems].view(torch.int32), s[self.o_un:self.o_un + self.cap_elems],
+                s[self.o_shp:self.o_shp + 16 * self.cap_pairs].view(torch.int64).view(-1, 2),
+                s[self.o_meta:self.o_meta + 16].view(torch.int64))
+
+    def reserve(self, total, n_pairs):
+        """Collective.  Makes every slab hold max-over-ranks (total, n_pairs); one 16-byte all-reduce."""
+        self._need.copy_(torch.tensor([int(total), int(n_pairs)], dtype=torch.int64))
+        dist.all_reduce(self._need, op=dist.ReduceOp.MAX, group=self.group)
+        need_e, need_p = (int(v) for v in self._need.cpu())
+        if need_e > self.cap_elems or need_p > self.cap_pairs:
+            torch.cuda.synchronize(self.device)
+            dist.barrier(self.group)                  # nobody still writes into the old slabs
+            self._alloc(max(need_e + need_e // 4, self.cap_elems), max(2 * need_p, self.cap_pairs))
+
+    def out_alloc(self, total, pairs):
+        self.reserve(total, len(pairs))
+        pl, un, _, _ = self._views(self.rank0, self.rank)
+        return pl, un, None
+
+    def publish(self, total, pair_shapes):
+        """pair_shapes int64 [n_pairs, 2] (host or device).  Ends the step on this rank."""
+        _, _, shp, meta = self._views(self.rank0, self.rank)
+        k = int(pair_shapes.shape[0])
+        if k:
+            shp[:k].copy_(pair_shapes.to(self.device, torch.int64).reshape(-1, 2), non_blocking=True)
+        meta.copy_(torch.tensor([int(total), k], dtype=torch.int64).to(self.device))
+        dist.all_reduce(self._need, op=dist.ReduceOp.MAX, group=self.group)   # stream-ordered after every rank's stores
+
+    def collect(self):
+        """rank 0, after ``publish``: [(path_len, unreachable, pair_shapes)] per rank (views of the slabs)."""
+        assert self.rank == 0
+        out = []
+        metas = torch.stack([self._views(self.buf, r)[3] for r in range(self.world)]).cpu()
+        for r in range(self.world):
+            pl, un, shp, _ = self._views(self.buf, r)
+            n, k = int(metas[r, 0]), int(metas[r, 1])
+            out.append((pl[:n], un[:n], shp[:k]))
+        return out
+
+
 def assemble(gathered, blocks, max_num_misses=1):
     """rank 0: {(t, t_bef): (path_len [n_pred,n_cur] int32 ndarray, unreachable uint8 ndarray)} over the
     whole timelapse, from ``gather_to_rank0`` output and the partition."""
@@ -77,9 +151,11 @@ def assemble(gathered, blocks, max_num_misses=1):
     return res
 
 
-def associate_sharded(Y, tile_yx, mask, max_px=500, max_num_misses=1, group=None, **kw):
+def associate_sharded(Y, tile_yx, mask, max_px=500, max_num_misses=1, group=None, slabs=None, **kw):
     """Each rank passes the WHOLE head tensor Y [T, ...] (or at least its own block + halo rows at
-    their global positions) and processes its block on its own GPU; rank 0 gets the assembled dict."""
+    their global positions) and processes its block on its own GPU; rank 0 gets the assembled dict.
+    ``slabs`` (a PeerSlabs, CUDA + NCCL): the kernels write into rank 0's memory directly; without
+    it the matrices are gathered with NCCL / gloo sends after the kernels."""
     from . import pipeline
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
@@ -87,7 +163,12 @@ def associate_sharded(Y, tile_yx, mask, max_px=500, max_num_misses=1, group=None
     blocks = partition(T, world, max_num_misses)
     first, own, stop = blocks[rank]
     res = pipeline.associate_frames(Y[first:stop], tile_yx, mask, max_px=max_px, max_num_misses=max_num_misses,
-                                    t0=own - first, want_cost=False, **kw)
+                                    t0=own - first, want_cost=False,
+                                    out_alloc=slabs.out_alloc if slabs is not None else None, **kw)
     shapes = torch.from_numpy(np.stack([res.pairs['n_src'], res.pairs['n_dst']], 1).astype(np.int64).reshape(-1, 2))
-    g = gather_to_rank0(res.path_len, res.unreachable, shapes, group)
+    if slabs is not None:
+        slabs.publish(res.path_len.numel(), shapes)
+        g = slabs.collect() if rank == 0 else None
+    else:
+        g = gather_to_rank0(res.path_len, res.unreachable, shapes, group)
     return (assemble(g, blocks, max_num_misses) if rank == 0 else None), res

@@ -233,14 +233,24 @@ def run_b200(args, wl):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     ctx = ops.get_context(dev)
 
+    # N > 1: the K2 kernels of every rank store their matrices straight into rank 0's HBM over NVLink
+    # (sharding.PeerSlabs); --gather nccl = send them after the kernels instead (the round-1 baseline)
+    slabs = sharding.PeerSlabs(dev) if world > 1 and args.gather == 'peer' else None
+
     def gather_to_rank0(res):
         if world == 1:
             return
         shapes = torch.from_numpy(np.stack([res.pairs['n_src'], res.pairs['n_dst']], 1).astype(np.int64).reshape(-1, 2))
-        sharding.gather_to_rank0(res.path_len, res.unreachable, shapes)
+        if slabs is not None:
+            slabs.publish(res.path_len.numel(), shapes)
+            if rank == 0:
+                slabs.collect()
+        else:
+            sharding.gather_to_rank0(res.path_len, res.unreachable, shapes)
 
     def step():
-        res = pipeline.associate_frames(Yd, td, md, max_px=MAX_PX, max_num_misses=MAX_MISSES, want_cost=False, t0=t0)
+        res = pipeline.associate_frames(Yd, td, md, max_px=MAX_PX, max_num_misses=MAX_MISSES, want_cost=False, t0=t0,
+                                        out_alloc=slabs.out_alloc if slabs is not None else None)
         gather_to_rank0(res)
         return res
 
@@ -391,7 +401,7 @@ def run_b200(args, wl):
                     scaling='weak', vs_baseline=None, dtype='int32', data='synthetic',
                     config=dict(workload=wl['desc'], frames_per_gpu=wl['T'], frame_pairs_total=int(total_pairs),
                                 dets_per_frame=float(np.mean(n_out)), max_px=MAX_PX, max_num_misses=MAX_MISSES,
-                                parallelism=f'timepoint shards x{world}, gather to rank 0', l2='flushed between timed steps (256 MiB write)'),
+                                parallelism=f'timepoint shards x{world}, ' + ('single GPU' if world == 1 else 'K2 stores into rank 0 HBM over NVLink (peer slabs)' if slabs is not None else 'NCCL gather to rank 0'), l2='flushed between timed steps (256 MiB write)'),
                     e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu)
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -462,6 +472,8 @@ def main():
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c5'])
     ap.add_argument('--cpu-calls', type=int, default=1200, help='in-range A* calls of the cpu_baseline sample (~15 ms each at 2048^2)')
     ap.add_argument('--ref-calls', type=int, default=250, help='in-range A* calls per --impl reference step')
+    ap.add_argument('--gather', default='peer', choices=['peer', 'nccl'],
+                    help='N > 1: K2 writes into rank 0 memory over NVLink (peer) or NCCL sends after the kernels (nccl)')
     ap.add_argument('--max-px', type=int, default=500,
                     help='max_px_assoc_dist (SURVEY 8d: configs[2] is also swept at 1000; > 511 runs the wide all-levels kernel)')
     args = ap.parse_args()
