@@ -223,6 +223,7 @@ def run_b200(args, wl):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')     # stdout carries the one JSON line only
         dist.init_process_group('nccl', device_id=dev)
 
     mask, Y, tile_yx, t0 = make_block(wl, rank)
