@@ -70,3 +70,45 @@ def test_gather_gloo(world, tmp_path):
     T = 7
     mp.spawn(_worker, args=(world, _free_port(), T, out), nprocs=world, join=True)
     assert open(out).read() == 'ok %d' % len(frame_pair_keys(T, 1))
+
+
+def _peer_worker(rank, world, port, out_path):
+    """One NCCL rank on cuda:0: PeerSlabs as the kernels' output (slab layout, collective growth,
+    publish / collect) against the plain single-process result."""
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(0)
+    dev = torch.device('cuda', 0)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    try:
+        from axtrack_b200 import pipeline
+        H, W, T = 700, 800, 6
+        mask = synth.make_mask(H, W, seed=3)
+        tt = synth.tile_table(H, W)
+        rng = np.random.default_rng(2)
+        fg = np.argwhere(mask)
+        Y = np.stack([synth.make_head_tensor(fg[rng.integers(0, len(fg), 60)], H, W, seed=10 + t)[0] for t in range(T)])
+        Yd, td = torch.from_numpy(Y).to(dev), torch.from_numpy(tt).to(dev)
+        md = torch.from_numpy(mask.astype(np.uint8)).to(dev)
+        ref = pipeline.associate_frames(Yd, td, md, want_cost=False).pair_matrices()
+        slabs = sharding.PeerSlabs(dev, cap_elems=64, cap_pairs=2)            # far too small: must grow
+        for _ in range(2):
+            got, _ = sharding.associate_sharded(Yd, td, md, slabs=slabs)
+            assert set(got) == set(ref) and len(got) == 2 * T - 3
+            for k in ref:
+                assert np.array_equal(got[k][0], ref[k][0]) and np.array_equal(got[k][1], ref[k][1]), k
+        assert slabs.cap_elems >= sum(v[0].size for v in ref.values())
+        open(out_path, 'w').write('ok %d' % len(got))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_peer_slabs_single_rank(tmp_path):
+    """The N > 1 product path (kernels store into rank 0's symmetric-memory slab) with world_size 1
+    on one GPU; the 2- and 8-GPU runs are scratch/peer_check.py and bench.py --gpus N."""
+    if not torch.cuda.is_available():
+        pytest.fail('-m gpu tests need a CUDA device')
+    out = str(tmp_path / 'ok.txt')
+    mp.spawn(_peer_worker, args=(1, _free_port(), out), nprocs=1, join=True)
+    assert open(out).read().startswith('ok ')
