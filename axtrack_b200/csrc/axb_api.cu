@@ -435,6 +435,20 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     return AXB_OK;
 }
 
+int axb_feature_hist(axb_ctx* c, const float* image_dev, int H, int W, const int32_t* boxes_dev, int n_boxes,
+                     int bins, float lo, float hi, float* out_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (H <= 0 || W <= 0 || n_boxes < 0 || bins < 1 || bins > AXB_MAX_BINS || !(hi > lo))
+        return bad_arg(c, "axb_feature_hist: bad size, bins outside [1, AXB_MAX_BINS] or empty range");
+    if (n_boxes == 0) return AXB_OK;
+    if (!image_dev || !boxes_dev || !out_dev) return bad_arg(c, "axb_feature_hist: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    axb::launch_k5(image_dev, H, W, boxes_dev, n_boxes, bins, lo, hi, out_dev, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
 int axb_transition_cost_batch(axb_ctx* c, const int32_t* path_len_dev, const axb_pair_desc* pairs_dev, int n_pairs,
                               int max_elems_per_pair, const double* cost_tab_dev, const int64_t* arc_tab_dev,
                               int n_gaps, int max_px, double* cost_dev, int64_t* arc_dev, void* stream) {

@@ -121,6 +121,9 @@ void launch_k3(const int32_t* path_len, const axb_pair_desc* pairs, int n_pairs,
                const long long* arc_tab, int n_gaps, int max_px, double* cost, long long* arc,
                unsigned long long* err_flags, int max_elems_per_pair, cudaStream_t stream);
 
+void launch_k5(const float* image, int H, int W, const int32_t* boxes, int n_boxes, int bins, float lo, float hi,
+               float* out, cudaStream_t stream);
+
 // ---- K1 ------------------------------------------------------------------------------------
 struct K1Params {
     const float* Y;              // [F][ntiles][Sx][Sy][3]

@@ -39,7 +39,7 @@
 #include <cassert>
 #define AXB_ASSERT(c) assert(c)
 #else
-#define AXB_ASSERT(c) do { } while (0)
+#define AXB_ASSERT(c) ((void)0)
 #endif
 
 namespace axb {

@@ -68,3 +68,21 @@ def transition_model(**kwargs):
     cost, _ = ops.transition_cost_batch(pl, pairs, tab[None, :])
     ops.raise_status(device=dev)
     return cost.cpu().numpy().reshape(n, m)
+
+
+def feature_model(**kwargs):
+    """Drop-in for mincostflow_models.feature_model (mincostflow_models.py:30-64): 180-bin
+    histograms of the image crops under the boxes, min-max normalised -> float32 (N, 180, 1);
+    ``np.zeros((0,))`` for no boxes, like the reference.  ``image`` may be a numpy array (copied to
+    the current CUDA device once per call) or a CUDA tensor; ``boxes`` (N, 4) rows (x, y, w, h)."""
+    import torch
+    from . import ops
+    assert 'image' in kwargs and 'boxes' in kwargs, 'Parameters must contail image and boxes'
+    boxes, image = kwargs['boxes'], kwargs['image']
+    if len(boxes) == 0:
+        return np.zeros((0,))
+    dev = image.device if isinstance(image, torch.Tensor) and image.is_cuda else torch.device('cuda', torch.cuda.current_device())
+    img = image if isinstance(image, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(image, dtype=np.float32))
+    b = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(np.asarray(boxes)), dtype=np.int32))
+    feats = ops.feature_hist(img.to(dev, torch.float32), b.to(dev))
+    return feats.cpu().numpy()[:, :, None]

@@ -243,3 +243,23 @@ def trace_paths(mask_bits, W, requests, max_px=500):
         ctx.check(ctx.lib.axb_trace_paths(ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), req.ctypes.data, n,
                                           int(max_px), yx.data_ptr(), ln.data_ptr(), _stream()))
     return yx, ln
+
+
+def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
+    """Appearance features of the boxes of one frame (K5).
+
+    image float32 CUDA [H, W]; boxes int32 CUDA [n, 4] rows (x, y, w, h).  -> float32 CUDA [n, bins]:
+    cv2.calcHist([crop], [0], None, [bins], [lo, hi]) min-max normalised, exactly as
+    mincostflow_models.feature_model computes it (mincostflow_models.py:30-64)."""
+    image = _need_cuda(image, 'image', torch.float32)
+    assert image.dim() == 2, 'image must be one [H, W] frame'
+    boxes = _need_cuda(boxes.reshape(-1, 4), 'boxes', torch.int32)
+    n = boxes.shape[0]
+    dev = image.device
+    ctx = get_context(dev)
+    out = torch.empty((n, int(bins)), dtype=torch.float32, device=dev)
+    if n:
+        H, W = image.shape
+        ctx.check(ctx.lib.axb_feature_hist(ctx.handle, image.data_ptr(), int(H), int(W), boxes.data_ptr(), n,
+                                           int(bins), float(lo), float(hi), out.data_ptr(), _stream()))
+    return out

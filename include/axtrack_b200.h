@@ -180,6 +180,19 @@ int axb_trace_paths(axb_ctx* ctx, const uint32_t* mask_bits_dev, int n_masks, in
                     const int32_t* req_host, int n_req, int max_px,
                     int32_t* path_yx_dev, int32_t* path_len_dev, void* stream);
 
+/* ---- appearance features ------------------------------------------------
+ * Replaces mincostflow_models.feature_model (mincostflow_models.py:30-64): per box (x, y, w, h)
+ * of boxes_dev int32 [n][4], the histogram of the image crop image[max(y,0) : max(y0+1, y0+h),
+ * max(x,0) : max(x0+1, x0+w)] (clipped at the image border like the numpy slice) over `bins`
+ * uniform bins of [lo, hi) as cv2.calcHist computes it, min-max normalised to [0, 1] as
+ * cv2.normalize(..., NORM_MINMAX) does (OpenCV 4.x float arithmetic, fused multiply-add).
+ * image_dev float32 [H][W] (one frame, Timelapse.get_frame_and_truedets(t)[0][0]);
+ * out_dev float32 [n][bins] (the reference's (n, bins, 1) array).  bins <= AXB_MAX_BINS. */
+#define AXB_MAX_BINS 1024
+int axb_feature_hist(axb_ctx* ctx, const float* image_dev, int H, int W,
+                     const int32_t* boxes_dev, int n_boxes, int bins, float lo, float hi,
+                     float* out_dev, void* stream);
+
 /* ---- transition costs ------------------------------------------------------------------
  * Replaces the arithmetic of mincostflow_models.transition_model (mincostflow_models.py:100-119)
  * and the arc cost int(multi_factor * cost) of libmot's graph builder

@@ -291,3 +291,30 @@ def transition_cost(path_len, max_px=500, miss_rate=0.6, time_gap=1, vis_sim_wei
                     + vis_sim_weight * vis_sim + 1e-6)
     costs[inf_dist] = np.inf
     return costs
+
+
+def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
+    """mincostflow_models.py:30-64 (feature_model) without cv2: the crop of each box (x, y, w, h),
+    cv2.calcHist over `bins` uniform bins of [lo, hi) -- idx = floor(double(v)*a + b), a = bins/(hi-lo),
+    b = -lo*a -- and cv2.normalize(NORM_MINMAX, 0, 1): scale = float(1/(max-min)) (0 when max-min <=
+    DBL_EPSILON), shift = 0.f - float(min*scale), feature = fma(count, scale, shift) rounded once to
+    float32 (OpenCV 4.x; pinned against cv2 4.13 by tests/golden/feature_hist_*.npz).  -> float32 [n, bins]."""
+    image = np.asarray(image, np.float32)
+    boxes = np.atleast_2d(np.asarray(boxes)).astype(np.int64)
+    a = bins / (float(hi) - float(lo))
+    b = -float(lo) * a
+    out = np.zeros((len(boxes), bins), np.float32)
+    for i, roi in enumerate(boxes):
+        x1, x2 = max(int(roi[1]), 0), max(int(roi[0]), 0)
+        x3, x4 = max(x1 + 1, x1 + int(roi[3])), max(x2 + 1, x2 + int(roi[2]))
+        v = image[x1:x3, x2:x4].astype(np.float64).ravel()
+        with np.errstate(invalid='ignore'):
+            idx = np.floor(v * a + b)
+            idx[np.isnan(v)] = 0          # observed: cv2.calcHist counts a NaN pixel in bin 0 (any range)
+            ok = (idx >= 0) & (idx < bins)
+        cnt = np.bincount(idx[ok].astype(np.int64), minlength=bins).astype(np.float32)
+        smin, smax = float(cnt.min()), float(cnt.max())
+        scale = float(np.float32(1.0 / (smax - smin) if smax - smin > np.finfo(np.float64).eps else 0.0))
+        shift = float(np.float32(0.0) - np.float32(smin * scale))
+        out[i] = (cnt.astype(np.float64) * scale + shift).astype(np.float32)   # exact product + one rounding = fma
+    return out
