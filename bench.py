@@ -330,6 +330,21 @@ def run_b200(args, wl):
             k3ms.append(e0.elapsed_time(e1))
     yx_h = det['yx'].cpu().numpy()
     frame_dets = [yx_h[t, :int(n_out[t])] for t in range(len(n_out))]
+    # K5 (feature_model histograms): the 70x70 boxes of every frame of the block on a
+    # synthetic float32 frame, one launch per frame as libmot calls it; beside the metric, not inside it
+    k5ms = []
+    frame_img = torch.rand((H, W), dtype=torch.float32, device=dev)
+    box_t = [torch.from_numpy(np.concatenate([fd[:, ::-1] - 35, np.full((len(fd), 2), 70)], 1).astype(np.int32)).to(dev)
+             for fd in frame_dets]
+    for i in range(3 + args.steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for b in box_t:
+            ops.feature_hist(frame_img, b)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            k5ms.append(e0.elapsed_time(e1))
     alg = algorithmic_bytes(frame_dets, res.keys, H, W, MAX_PX)
     k2 = float(np.mean(k2ms)) * 1e-3
     peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
@@ -348,7 +363,7 @@ def run_b200(args, wl):
     roofline = dict(bound='hbm', kernel=klabel,
                     achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
                     peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
-                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)),
+                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)), k5_feature_hist_ms=float(np.mean(k5ms)),
                     traffic=traffic)
 
     # ---- e2e: host buffers through the C ABI ------------------------------------------------------
