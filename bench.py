@@ -204,7 +204,7 @@ def run_reference(args, wl):
                 config=dict(workload=wl['desc'], max_px=MAX_PX, max_num_misses=MAX_MISSES),
                 cpu_baseline=dict(value=v, unit='frame-pairs/s', cores=cores, kind=kind, sample=sample),
                 e2e=dict(value=v, unit='frame-pairs/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------
@@ -223,7 +223,6 @@ def run_b200(args, wl):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')     # stdout carries the one JSON line only
         dist.init_process_group('nccl', device_id=dev)
 
     mask, Y, tile_yx, t0 = make_block(wl, rank)
@@ -414,12 +413,12 @@ def run_b200(args, wl):
     if rank == 0:
         line = dict(metric='frame-pairs/sec (A* cost matrix + decode/NMS)', value=value, unit='frame-pairs/s', n_gpus=world,
                     steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms / args.steps, higher_is_better=True,
-                    scaling='weak', vs_baseline=None, dtype='int32', data='synthetic',
+                    scaling=args.scaling, vs_baseline=None, dtype='int32', data='synthetic',
                     config=dict(workload=wl['desc'], frames_per_gpu=wl['T'], frame_pairs_total=int(total_pairs),
                                 dets_per_frame=float(np.mean(n_out)), max_px=MAX_PX, max_num_misses=MAX_MISSES,
                                 parallelism=f'timepoint shards x{world}, ' + ('single GPU' if world == 1 else 'K2 stores into rank 0 HBM over NVLink (peer slabs)' if slabs is not None else 'NCCL gather to rank 0'), l2='flushed between timed steps (256 MiB write)'),
                     e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -475,11 +474,25 @@ def run_c5(args):
                 roofline=dict(bound='hbm', kernel='k1_decode_nms_kernel', achieved=headline['gbs'], peak=peak, unit='GB/s', frac=headline['frac'],
                               note='one CTA per frame: latency bound below ~148 frames per launch'),
                 sweep=sweep)
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_OUT = None
+
+
+def emit(line):
+    """The one JSON line, on the process's original stdout."""
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + '\n')
+    out.flush()
 
 
 def main():
-    global MAX_PX
+    global MAX_PX, _JSON_OUT
+    # stdout carries the JSON line only: whatever libraries print on fd 1 (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
@@ -488,6 +501,8 @@ def main():
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c5'])
     ap.add_argument('--cpu-calls', type=int, default=1200, help='in-range A* calls of the cpu_baseline sample (~15 ms each at 2048^2)')
     ap.add_argument('--ref-calls', type=int, default=250, help='in-range A* calls per --impl reference step')
+    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
+                    help="weak: the workload's T frames per GPU (default); strong: T frames in total, T/N per GPU")
     ap.add_argument('--gather', default='peer', choices=['peer', 'nccl'],
                     help='N > 1: K2 writes into rank 0 memory over NVLink (peer) or NCCL sends after the kernels (nccl)')
     ap.add_argument('--max-px', type=int, default=500,
@@ -497,6 +512,9 @@ def main():
     if args.workload == 'c5':
         return run_c5(args)
     wl = WORKLOADS[args.workload]
+    if args.scaling == 'strong':       # configs[3]: ONE timelapse of T frames sharded by timepoint over the ranks
+        world = int(os.environ.get('WORLD_SIZE', '1'))
+        wl = dict(wl, T=-(-wl['T'] // world), desc=wl['desc'] + f' -- {wl["T"]} frames in total, sharded over {world} GPU(s)')
     if args.impl == 'reference':
         run_reference(args, wl)
     else:
