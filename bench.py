@@ -235,7 +235,16 @@ def run_b200(args, wl):
 
     # N > 1: the K2 kernels of every rank store their matrices straight into rank 0's HBM over NVLink
     # (sharding.PeerSlabs); --gather nccl = send them after the kernels instead (the round-1 baseline)
-    slabs = sharding.PeerSlabs(dev) if world > 1 and args.gather == 'peer' else None
+    slabs = None
+    if world > 1 and args.gather == 'peer':
+        try:
+            slabs = sharding.PeerSlabs(dev)
+        except Exception as e:                       # no peer mapping on this box: every rank falls back together
+            print(f'[bench] rank {rank}: peer slabs unavailable ({e!r}); using the NCCL gather', file=sys.stderr)
+        ok = torch.tensor([1 if slabs is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            slabs = None
 
     def gather_to_rank0(res):
         if world == 1:
