@@ -22,7 +22,8 @@ constexpr int kMaxChain = 4;          // frame pairs that share one source searc
 constexpr int kHashSize = 1024;       // target-cell hash (u32 entries) in shared memory
 constexpr int kHashMaxLoad = 640;     // candidates per search pass
 constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
-constexpr int kK2Threads = 256;       // one CTA (8 warps) per source search
+constexpr int kK2Threads = 256;       // wide all-levels kernel: one CTA (8 warps) per source search
+constexpr int kGenThreads = 512;      // all-levels kernel (one CTA per SM): 16 warps per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
 constexpr int kSeedCalWide = 1024;
 constexpr int kFastMaxPx = 511;       // largest radius of the 1024-column folded window (tile-word kernels, shared-memory bitmaps)

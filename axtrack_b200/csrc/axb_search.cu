@@ -22,7 +22,7 @@
 // Mapping to the SM.  A search is ~max_px dependent wavefronts of a few hundred cells: latency
 // bound.  The level-0 searches (nearly all sources on real data) run on the tile-word kernels of
 // axb_search_fast.cu; this file holds
-//   k2_general_kernel       all levels, one CTA of kK2Threads (8 warps) per source, one lane per
+//   k2_general_kernel       all levels, one CTA of kGenThreads (16 warps) per source, one lane per
 //                           (frontier cell, direction): per-cell bitmaps "open mask pixel" and
 //                           "open off-mask pixel" in shared memory (folded-diamond layout of
 //                           axb_common.cuh, rows rotated by their index over the 32 banks),
@@ -195,6 +195,7 @@ template <bool GEN, int NT, bool WIDE>
 __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
     using G = Geo<WIDE>;
     constexpr int kCal = G::CAL;
+    static_assert(NT <= kHashMaxLoad, "a group of NT targets must fit one pass of the target hash");
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const uint32_t lt = lanemask_lt();
@@ -445,7 +446,7 @@ __device__ __forceinline__ void general_body(const K2Params& p, uint32_t* smem, 
         const int t = ctl.item;
         if (t >= total) break;
         const int item = p.gen_list[t];
-        run_item<true, kK2Threads, WIDE>(p, item, smem, gscr, ctl);
+        run_item<true, WIDE ? kK2Threads : kGenThreads, WIDE>(p, item, smem, gscr, ctl);
         if (p.trace_par) {             // one (source, target) request per pair: walk the entry directions back
             __syncthreads();
             if (threadIdx.x == 0) {
@@ -473,7 +474,7 @@ __device__ __forceinline__ void general_body(const K2Params& p, uint32_t* smem, 
     }
 }
 
-__global__ void __launch_bounds__(kK2Threads, 1) k2_general_kernel(const K2Params p) {
+__global__ void __launch_bounds__(kGenThreads, 1) k2_general_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     general_body<false>(p, smem, ctl);
@@ -579,7 +580,7 @@ void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {
     if (first_use_on_device(attr_set)) {
         cudaFuncSetAttribute(k2_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_gen_smem_bytes(kFastMaxPx));
     }
-    k2_general_kernel<<<grid, kK2Threads, k2_gen_smem_bytes(p.max_px), stream>>>(p);
+    k2_general_kernel<<<grid, kGenThreads, k2_gen_smem_bytes(p.max_px), stream>>>(p);
 }
 
 void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream) {
