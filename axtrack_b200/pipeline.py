@@ -24,12 +24,20 @@ def frame_pair_keys(T, max_num_misses=1, t0=0):
 
 
 def build_pairs(n_out, cap, keys, mask_of_frame=None):
-    """Pair descriptors for detections stored as [F, cap, 2]: frame f's rows start at f*cap."""
-    entries = []
-    for t, tb in keys:
-        m = 0 if mask_of_frame is None else int(mask_of_frame[t])
-        entries.append((m, tb * cap, int(n_out[tb]), t * cap, int(n_out[t]), t - tb))
-    return ops.make_pairs(entries)
+    """Pair descriptors for detections stored as [F, cap, 2]: frame f's rows start at f*cap.
+    Vectorised: this runs on the host between K1 and K2 while the GPU waits."""
+    k = np.asarray(keys, np.int64).reshape(-1, 2)
+    t, tb = k[:, 0], k[:, 1]
+    n_out = np.asarray(n_out, np.int64)
+    arr = np.zeros(len(k), dtype=_lib.PAIR_DTYPE)
+    ns, nd = n_out[tb], n_out[t]
+    arr['mask_idx'] = 0 if mask_of_frame is None else np.asarray(mask_of_frame, np.int64)[t]
+    arr['src_off'], arr['n_src'] = tb * cap, ns
+    arr['dst_off'], arr['n_dst'] = t * cap, nd
+    arr['time_gap'] = t - tb
+    sizes = ns * nd
+    arr['out_off'] = np.cumsum(sizes) - sizes
+    return arr, int(sizes.sum()), int(ns.sum())
 
 
 class Association:
