@@ -647,10 +647,11 @@ void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
         cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
         cudaFuncSetAttribute(k2_sparse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     }
-    // A launch that leaves at least half of the CTA slots empty is latency bound and has shared
-    // memory to spare: the target hash moves from the CTA's global scratch into shared memory and
-    // the window capacity grows to what the launch's residency leaves (up to the whole folded
-    // diamond, so that no window needs the dense kernel's second pass).
+    // A launch that does not fill the CTA slots has shared memory to spare: the window capacity
+    // grows to what the launch's residency leaves (up to the whole folded diamond, so that fewer or
+    // no windows need the dense kernel's second pass), and when at least half of the slots stay
+    // empty (latency counts, not residency) the target hash moves from the CTA's global scratch
+    // into shared memory as well.
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -658,16 +659,20 @@ void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
     q.hash_smem = 0;
     q.sparse_words = kSparseWords;
     size_t smem = k2_sparse_smem_bytes(p.max_px);
-    if (2 * grid <= sms * kSparseCtasPerSm) {
-        const int per_sm = (grid + sms - 1) / sms;
-        const size_t fixed = smem - (size_t)kSparseWords * sizeof(uint32_t) + kSparseHash * sizeof(uint32_t);
+    const int per_sm = (grid + sms - 1) / sms;
+    if (per_sm < kSparseCtasPerSm) {
+        q.hash_smem = 2 * per_sm <= kSparseCtasPerSm ? 1 : 0;
+        const size_t fixed = smem - (size_t)kSparseWords * sizeof(uint32_t) + (q.hash_smem ? kSparseHash * sizeof(uint32_t) : 0);
         const size_t budget = (size_t)227 * 1024 / per_sm - 1024;
         const size_t full = (size_t)k2_tile_rows(p.max_px) * 128;
         size_t words = (budget - fixed) / sizeof(uint32_t) & ~(size_t)3;
         if (words > full) words = full;
-        q.hash_smem = 1;
-        q.sparse_words = (int)words;
-        smem = fixed + words * sizeof(uint32_t);
+        if (words > (size_t)kSparseWords) {
+            q.sparse_words = (int)words;
+            smem = fixed + words * sizeof(uint32_t);
+        } else {
+            q.hash_smem = 0;
+        }
     }
     k2_sparse_kernel<<<grid, kFastThreads, smem, stream>>>(q);
 }

@@ -325,7 +325,7 @@ def test_sparse_window_multi_pass_and_dense_fallback(cuda):
     dst = fg[rng.integers(0, len(fg), 2500)].astype(np.int32)
     _check(_gpu_cost(cuda, mask, src, dst, 500), oracle.cost_matrix_rule(mask, src, dst, 500), 'sparse multi-pass')
     # the same with enough sources to fill the CTA slots (small windows, target hash in global scratch)
-    src = fg[rng.integers(0, len(fg), 800)].astype(np.int32)
+    src = fg[rng.integers(0, len(fg), 1500)].astype(np.int32)
     _check(_gpu_cost(cuda, mask, src, dst[:1200], 500), oracle.cost_matrix_rule(mask, src, dst[:1200], 500), 'sparse multi-pass, full launch')
     ones = np.ones((H, W), np.uint8)
     ones[300:800, 600] = 0
@@ -334,9 +334,9 @@ def test_sparse_window_multi_pass_and_dense_fallback(cuda):
     for max_px in (500, 511, 130):
         _check(_gpu_cost(cuda, ones, src, dst, max_px), oracle.cost_matrix_rule(ones, src, dst, max_px), ('dense', max_px))
     # (c) a launch that fills the CTA slots keeps the small sparse windows (a small launch grows them
-    # to what its residency leaves): 800 open-field sources at radius 300 overflow them -> dense kernel
-    src = np.stack([rng.integers(0, H, 800), rng.integers(0, W, 800)], 1).astype(np.int32)
-    dst = np.stack([rng.integers(0, H, 60), rng.integers(0, W, 60)], 1).astype(np.int32)
+    # to what its residency leaves): 1500 open-field sources at radius 300 overflow them -> dense kernel
+    src = np.stack([rng.integers(0, H, 1500), rng.integers(0, W, 1500)], 1).astype(np.int32)
+    dst = np.stack([rng.integers(0, H, 40), rng.integers(0, W, 40)], 1).astype(np.int32)
     _check(_gpu_cost(cuda, ones, src, dst, 300), oracle.cost_matrix_rule(ones, src, dst, 300), 'dense, full launch')
 
 
