@@ -160,7 +160,7 @@ struct Ctl {
     int cnt[3];        // frontier sizes, rotating: wave s reads cnt[s%3], appends to cnt[(s+1)%3]
     int unsettled;     // in-range targets not yet reached
     int ncand;
-    int seedcnt;       // general: seeds appended for the next level
+    int seedadd[3];    // general: seeds appended for the next level per wave, rotating like cnt[]
     int settled[3];    // targets reached per wave, rotating like cnt[]
     int item;
 };
@@ -315,7 +315,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                 ctl.cnt[0] = GEN ? 0 : 1; ctl.cnt[1] = 0; ctl.cnt[2] = 0;
                 ctl.settled[0] = 0; ctl.settled[1] = 0; ctl.settled[2] = 0;
                 ctl.unsettled = ncand;
-                ctl.seedcnt = 0;
+                ctl.seedadd[0] = 0; ctl.seedadd[1] = 0; ctl.seedadd[2] = 0;
             }
             if (GEN) for (int jj = tid; jj < kCal; jj += NT) cal0[jj] = 1;    // the source: one seed tagged j = 0
             __threadfence_block();
@@ -339,14 +339,14 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                     int j = 0;
                     while (cal_cur[j] == 0) ++j;                      // first seeded j of this level
                     const int jstart = j;
-                    int sp = 0, nlist = 0, step = 0;
+                    int sp = 0, nlist = 0, step = 0, seed_total = 0;
                     bool hit = false;
                     for (;;) {
                         const int send = cal_cur[j];
                         const int tot_n = nlist + (send - sp);
                         if (tot_n == 0) {
                             if (sp >= n_seeds) break;                 // level exhausted
-                            if (tid == 0) cal_nxt[j] = ctl.seedcnt;
+                            if (tid == 0) cal_nxt[j] = seed_total;
                             ++j;
                             continue;
                         }
@@ -358,6 +358,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                         uint32_t* const gnxt = gq0 + (size_t)((step + 1) & 1) * GQCAP;
                         int* const cnt_nxt = &ctl.cnt[(step + 1) % 3];
                         int* const set_nxt = &ctl.settled[(step + 1) % 3];
+                        int* const seed_nxt = &ctl.seedadd[(step + 1) % 3];
                         const int ntask = tot_n * 4;
                         for (int base = (tid & ~31); base < ntask; base += NT) {
                             const int i = (base + lane) >> 2;
@@ -398,7 +399,7 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                             }
                             if (bb) {
                                 int pos = 0;
-                                if (lane == 0) pos = atomicAdd(&ctl.seedcnt, __popc(bb));
+                                if (lane == 0) pos = seed_total + atomicAdd(seed_nxt, __popc(bb));
                                 pos = __shfl_sync(kFull, pos, 0);
                                 if (got_bg) gs_nxt[pos + __popc(bb & lt)] = ne;
                             }
@@ -407,21 +408,22 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
                         __syncthreads();
                         nlist = *cnt_nxt;
                         unsettled -= *set_nxt;
-                        if (tid == 0) { ctl.cnt[step % 3] = 0; ctl.settled[step % 3] = 0; cal_nxt[j] = ctl.seedcnt; }
-                        __syncthreads();       // seedcnt is read before the next wave appends to it
+                        seed_total += *seed_nxt;           // CTA-uniform running count of the next level's seeds
+                        if (tid == 0) { ctl.cnt[step % 3] = 0; ctl.settled[step % 3] = 0; ctl.seedadd[step % 3] = 0; cal_nxt[j] = seed_total; }
+                        // one barrier per wave: every counter a wave appends to rotates over three slots
                         sp = send;
                         ++step;
                         ++j;
                     }
                     // ---- level end: complete the next level's calendar ------------------------------
                     __syncthreads();
-                    const int total_next = ctl.seedcnt;
+                    const int total_next = seed_total;
                     for (int jj = tid; jj < kCal; jj += NT) {
                         if (jj >= j) cal_nxt[jj] = total_next;
                         else if (jj < jstart) cal_nxt[jj] = 0;
                     }
                     __syncthreads();
-                    if (tid == 0) { ctl.seedcnt = 0; ctl.cnt[0] = 0; ctl.cnt[1] = 0; ctl.cnt[2] = 0; ctl.settled[0] = 0; ctl.settled[1] = 0; ctl.settled[2] = 0; }
+                    if (tid == 0) { ctl.seedadd[0] = 0; ctl.seedadd[1] = 0; ctl.seedadd[2] = 0; ctl.cnt[0] = 0; ctl.cnt[1] = 0; ctl.cnt[2] = 0; ctl.settled[0] = 0; ctl.settled[1] = 0; ctl.settled[2] = 0; }
                     __syncthreads();
                     if (hit) break;                    // k* = k: every deeper target stays None
                     n_seeds = total_next;
