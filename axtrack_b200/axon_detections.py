@@ -110,11 +110,24 @@ class B200AssociationMixin:
         else:
             self._yolo_targets, heads = [], []
             print(f'Detecting axons in {self.dataset.name} data: ', end='\n')
-            for t in self.timepoint_subset:
-                X, yolo_target = self.dataset.get_frametiles_stack(t, self.device)
-                heads.append(self.model.detect_axons(X))          # PyTorch forward, unchanged (model.py:119-125)
-                self._yolo_targets.append(yolo_target)
-            self._pandas_tiled_dets, self._detections = self._decode_frames(torch.stack(heads))
+            fpf = getattr(self, 'frames_per_forward', None)
+            if fpf:
+                # opt-in K6 front end: tiles cut on the device from the dense X, `fpf` frames per forward
+                # (the forward's cuDNN algorithms may differ with the batch size, so head values are
+                # not guaranteed bit-identical to the one-frame-per-forward default below)
+                from .tiling import FrameTiler
+                ds = self.dataset
+                tiler = FrameTiler(ds.X.to_dense().to(self.device, torch.float32), ds.tilesize, ds.temporal_context,
+                                   ds.use_motion_filtered, ds.timepoints_indices)
+                Y = tiler.detect_frames(self.model, self.timepoint_subset, fpf)
+                self._yolo_targets = [ds.target_tiled[ds.timepoints_indices[t]].to(self.device) for t in self.timepoint_subset]
+            else:
+                for t in self.timepoint_subset:
+                    X, yolo_target = self.dataset.get_frametiles_stack(t, self.device)
+                    heads.append(self.model.detect_axons(X))          # PyTorch forward, unchanged (model.py:119-125)
+                    self._yolo_targets.append(yolo_target)
+                Y = torch.stack(heads)
+            self._pandas_tiled_dets, self._detections = self._decode_frames(Y)
             print('Done.\n', flush=True)
         if cache == 'to':
             self.to_cache('_yolo_targets', self._yolo_targets)

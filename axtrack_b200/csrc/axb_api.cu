@@ -467,6 +467,36 @@ int axb_transition_cost_batch(axb_ctx* c, const int32_t* path_len_dev, const axb
     return AXB_OK;
 }
 
+int axb_tile_nonempty(axb_ctx* c, const float* X_dev, int T, int C, int H, int W, int tilesize, uint8_t* nonempty_dev,
+                      void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (T < 0 || C < 1 || H <= 0 || W <= 0 || tilesize < 1 || T > 65535) return bad_arg(c, "axb_tile_nonempty: bad size");
+    if (T == 0) return AXB_OK;
+    if (!X_dev || !nonempty_dev) return bad_arg(c, "axb_tile_nonempty: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    axb::launch_k6_nonempty(X_dev, T, C, H, W, tilesize, nonempty_dev, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
+int axb_gather_frametiles(axb_ctx* c, const float* X_dev, int T, int C, int H, int W, int tilesize,
+                          const int32_t* tile_yx_dev, int ntiles, const int32_t* frames_dev, int n_frames,
+                          int temporal_context, int chan_lo, int chan_n, float* out_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (T <= 0 || C < 1 || H <= 0 || W <= 0 || tilesize < 1 || ntiles < 0 || n_frames < 0 || temporal_context < 0)
+        return bad_arg(c, "axb_gather_frametiles: bad size");
+    if (chan_lo < 0 || chan_n < 1 || chan_lo + chan_n > C) return bad_arg(c, "axb_gather_frametiles: channel range outside [0, C)");
+    if (ntiles == 0 || n_frames == 0) return AXB_OK;
+    if (!X_dev || !tile_yx_dev || !frames_dev || !out_dev) return bad_arg(c, "axb_gather_frametiles: NULL pointer");
+    AXB_CUDA(c, cudaSetDevice(c->device));
+    axb::launch_k6_gather(X_dev, T, C, H, W, tilesize, tile_yx_dev, ntiles, frames_dev, n_frames, temporal_context, chan_lo,
+                          chan_n, out_dev, c->status_dev + 1, c->num_sms, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
 int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     if (!c) return AXB_ERR_BAD_ARG;
     AXB_CUDA(c, cudaSetDevice(c->device));
@@ -497,6 +527,7 @@ int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     else if (flags & 2ull) rc = AXB_ERR_UNSUPPORTED_WEIGHT;
     else if (flags & 4ull) rc = AXB_ERR_CAPACITY;
     else if (flags & 8ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_transition_cost_batch: path length or time gap outside its table"; }
+    else if (flags & 16ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_gather_frametiles: a frame's temporal context leaves the timelapse"; }
     if (key != ~0ull || flags) {
         c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
         AXB_CUDA(c, cudaMemcpyAsync(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice, s));

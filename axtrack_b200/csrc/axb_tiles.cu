@@ -1,0 +1,99 @@
+// K6 -- tiling front end of the detector (sm_100a), SURVEY 8f rank 4.
+//
+// Replaces, for inference, the image half of Timelapse.construct_tiles (axtrack/Timelapse.py:508-525,
+// 539-558: torch.split into tilesize x tilesize tiles, ZeroPad2d at the right / bottom border, the
+// "non-empty tile" flags (X[:, :, :, 0] > 0).any(-1).any(-1)) and Timelapse.get_frametiles_stack
+// (Timelapse.py:150-157 over __getitem__ :111-125: per tile the temporal stack
+// X_tiled[t - tc : t + tc + 1, tile, channels].flatten(end_dim=1)), which the reference runs as a Python
+// loop over tiles per frame and one model forward per frame.  Here the timelapse X [T][C][H][W] stays
+// where it is in HBM (no X_tiled copy of the whole timelapse) and
+//   k6_nonempty_kernel  one CTA per (tile, frame): any(X[t][0][tile] > 0), early exit per 16 rows;
+//   k6_gather_kernel    writes the model input of a BATCH of frames [B][ntiles][(2tc+1)*nch][ts][ts]
+//                       straight from X, zero filled outside the image: a pure copy, 4 B read + 4 B
+//                       written per element, float4 when the rows allow it.  Both are HBM bound.
+#include "axb_common.cuh"
+
+namespace axb {
+
+__global__ void __launch_bounds__(256) k6_nonempty_kernel(const float* __restrict__ X, int T, int C, int H, int W, int ts,
+                                                          int xtiles, uint8_t* __restrict__ nonempty) {
+    const int tile = blockIdx.x, t = blockIdx.y;
+    const int ty = tile / xtiles, tx = tile - ty * xtiles;
+    const int y0 = ty * ts, x0 = tx * ts;
+    const int h = min(ts, H - y0), w = min(ts, W - x0);
+    const float* const img = X + ((size_t)t * C) * H * W;          // channel 0 of frame t
+    int any = 0;
+    for (int r0 = 0; r0 < h; r0 += 16) {
+        const int rows = min(16, h - r0);
+        int mine = 0;
+        for (int i = threadIdx.x; i < rows * w; i += blockDim.x) {
+            const int r = i / w, c = i - r * w;
+            mine |= img[(size_t)(y0 + r0 + r) * W + x0 + c] > 0.0f;
+        }
+        any = __syncthreads_or(mine);
+        if (any) break;
+    }
+    if (threadIdx.x == 0) nonempty[(size_t)tile * T + t] = (uint8_t)(any != 0);
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) k6_gather_kernel(const float* __restrict__ X, int T, int C, int H, int W, int ts,
+                                                        const int32_t* __restrict__ tile_yx, int ntiles,
+                                                        const int32_t* __restrict__ frames, int B, int tc, int chan_lo,
+                                                        int nch, int chunks, float* __restrict__ out,
+                                                        unsigned long long* err_flags) {
+    constexpr int ROWS = 16;
+    const int nst = 2 * tc + 1;
+    const long long n_planes = (long long)B * ntiles * nst * nch;
+    for (long long job = blockIdx.x; job < n_planes * chunks; job += gridDim.x) {
+        const long long plane = job / chunks;
+        const int chunk = (int)(job - plane * chunks);
+        long long q = plane;
+        const int ch = (int)(q % nch); q /= nch;
+        const int dt = (int)(q % nst); q /= nst;
+        const int tile = (int)(q % ntiles);
+        const int b = (int)(q / ntiles);
+        const int t = frames[b] + dt - tc;
+        const bool bad = t < 0 || t >= T;                         // CTA-uniform
+        if (bad && threadIdx.x == 0) atomicOr(err_flags, 16ull);
+        const int y0 = tile_yx[2 * tile] * ts, x0 = tile_yx[2 * tile + 1] * ts;
+        const float* const img = X + ((size_t)(bad ? 0 : t) * C + chan_lo + ch) * H * W;
+        float* const dst = out + (size_t)plane * ts * ts;
+        const int r_lo = chunk * ROWS, r_hi = min(ts, r_lo + ROWS);
+        if (VEC) {
+            const int wq = ts >> 2;
+            for (int i = threadIdx.x; i < (r_hi - r_lo) * wq; i += blockDim.x) {
+                const int r = r_lo + i / wq, c = (i % wq) << 2;
+                const int y = y0 + r, x = x0 + c;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!bad && y < H && x < W) v = __ldg(reinterpret_cast<const float4*>(img + (size_t)y * W + x));   // W % 4 == 0: all four in range
+                __stcs(reinterpret_cast<float4*>(dst + (size_t)r * ts + c), v);
+            }
+        } else {
+            for (int i = threadIdx.x; i < (r_hi - r_lo) * ts; i += blockDim.x) {
+                const int r = r_lo + i / ts, c = i % ts;
+                const int y = y0 + r, x = x0 + c;
+                dst[(size_t)r * ts + c] = (!bad && y < H && x < W) ? __ldg(img + (size_t)y * W + x) : 0.0f;
+            }
+        }
+    }
+}
+
+void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint8_t* nonempty, cudaStream_t stream) {
+    const int ytiles = (H + ts - 1) / ts, xtiles = (W + ts - 1) / ts;
+    const dim3 grid((unsigned)(ytiles * xtiles), (unsigned)T);
+    k6_nonempty_kernel<<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, nonempty);
+}
+
+void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,
+                      const int32_t* frames, int B, int tc, int chan_lo, int nch, float* out,
+                      unsigned long long* err_flags, int n_sms, cudaStream_t stream) {
+    const int chunks = (ts + 15) / 16;
+    const long long jobs = (long long)B * ntiles * (2 * tc + 1) * nch * chunks;
+    const int grid = (int)std::min<long long>(jobs, (long long)n_sms * 8 * 16);
+    const bool vec = (ts % 4 == 0) && (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
+    if (vec) k6_gather_kernel<true><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, tile_yx, ntiles, frames, B, tc, chan_lo, nch, chunks, out, err_flags);
+    else k6_gather_kernel<false><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, tile_yx, ntiles, frames, B, tc, chan_lo, nch, chunks, out, err_flags);
+}
+
+}  // namespace axb

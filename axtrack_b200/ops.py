@@ -186,7 +186,8 @@ def raise_status(pairs=None, dets_yx_host=None, device=None):
         raise ValueError('Start lies outside grid.')
     if rc == _lib.ERR_OOB_GOAL:
         raise ValueError('Goal lies outside grid.')
-    raise _lib.AxbError(rc, 'device-side status')
+    msg = ctx.lib.axb_last_error(ctx.handle).decode() if rc == _lib.ERR_BAD_ARG else ''
+    raise _lib.AxbError(rc, msg or 'device-side status')
 
 
 def transition_cost_batch(path_len, pairs, cost_tab, arc_tab=None, pairs_dev=None):
@@ -262,4 +263,55 @@ def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
         H, W = image.shape
         ctx.check(ctx.lib.axb_feature_hist(ctx.handle, image.data_ptr(), int(H), int(W), boxes.data_ptr(), n,
                                            int(bins), float(lo), float(hi), out.data_ptr(), _stream()))
+    return out
+
+
+#: USE_MOTION_DATA -> (first channel, number of channels) of X (Timelapse.py:116-124, 415-424)
+MOTION_CHANNELS = {'exclude': (0, 1), 'temp_context': (0, 1), 'only': (1, 2), 'include': (0, 3)}
+
+
+def tile_nonempty(X, tilesize=512):
+    """Non-empty tile flags of a dense timelapse (K6).
+
+    X float32 CUDA [T, C, H, W] -> bool CUDA [ytiles, xtiles, T] = ``tile_info[..., 0]`` of
+    Timelapse.construct_tiles (Timelapse.py:551)."""
+    X = _need_cuda(X, 'X', torch.float32)
+    assert X.dim() == 4, 'X must be [T, C, H, W]'
+    T, C, H, W = X.shape
+    yt, xt = -(-H // tilesize), -(-W // tilesize)
+    ctx = get_context(X.device)
+    out = torch.empty((yt * xt, T), dtype=torch.uint8, device=X.device)
+    ctx.check(ctx.lib.axb_tile_nonempty(ctx.handle, X.data_ptr(), int(T), int(C), int(H), int(W), int(tilesize),
+                                        out.data_ptr(), _stream()))
+    return out.view(yt, xt, T).bool()
+
+
+def compact_tiles(nonempty):
+    """int32 CUDA [ntiles, 2] rows (tile_y, tile_x) of the tiles that are non-empty at any t, row-major:
+    the order of X_tiled's tile axis (Timelapse.py:558) and of flat_tile_idx2yx_tile_idx (:141-148)."""
+    return torch.nonzero(nonempty.any(-1)).to(torch.int32).contiguous()
+
+
+def gather_frametiles(X, tile_yx, frames, tilesize=512, temporal_context=2, use_motion_filtered='exclude'):
+    """Model input of a batch of frames (K6): Timelapse.get_frametiles_stack (Timelapse.py:150-157) for
+    every raw frame index in ``frames`` at once.
+
+    X float32 CUDA [T, C, H, W]; tile_yx int32 CUDA [ntiles, 2]; frames int32 [B] (CUDA tensor, or any
+    sequence of raw frame indices = ``timepoints_indices[t]``, Timelapse.py:113).
+    -> float32 CUDA [B, ntiles, (2 * temporal_context + 1) * nch, tilesize, tilesize]."""
+    X = _need_cuda(X, 'X', torch.float32)
+    assert X.dim() == 4, 'X must be [T, C, H, W]'
+    tile_yx = _need_cuda(tile_yx.reshape(-1, 2), 'tile_yx', torch.int32)
+    if not isinstance(frames, torch.Tensor):
+        frames = torch.as_tensor(np.asarray(frames, np.int32).reshape(-1)).to(X.device)
+    frames = _need_cuda(frames.reshape(-1), 'frames', torch.int32)
+    lo, nch = MOTION_CHANNELS[use_motion_filtered]
+    T, C, H, W = X.shape
+    B, nt = frames.shape[0], tile_yx.shape[0]
+    ctx = get_context(X.device)
+    out = torch.empty((B, nt, (2 * int(temporal_context) + 1) * nch, int(tilesize), int(tilesize)),
+                      dtype=torch.float32, device=X.device)
+    ctx.check(ctx.lib.axb_gather_frametiles(ctx.handle, X.data_ptr(), int(T), int(C), int(H), int(W), int(tilesize),
+                                            tile_yx.data_ptr(), int(nt), frames.data_ptr(), int(B),
+                                            int(temporal_context), int(lo), int(nch), out.data_ptr(), _stream()))
     return out

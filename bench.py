@@ -353,6 +353,30 @@ def run_b200(args, wl):
         torch.cuda.synchronize()
         if i >= 3:
             k5ms.append(e0.elapsed_time(e1))
+    # K6 (tiling front end): non-empty tile flags of a 20-frame dense image block and the
+    # model input of 16 frames per launch (temporal context 2, USE_MOTION_DATA exclude); beside the metric
+    k6 = None
+    if H * W <= 4096 * 4096:
+        Tb, tcx = 20, 2
+        Xb = torch.rand((Tb, 1, H, W), dtype=torch.float32, device=dev)
+        fr = torch.arange(tcx, Tb - tcx, dtype=torch.int32, device=dev)
+        ne_ms, ga_ms = [], []
+        for i in range(3 + args.steps):
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0.record()
+            ne = ops.tile_nonempty(Xb, 512)
+            e1.record()
+            tyx = ops.compact_tiles(ne)
+            st = ops.gather_frametiles(Xb, tyx, fr, 512, tcx, 'exclude')
+            e2.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ne_ms.append(e0.elapsed_time(e1)); ga_ms.append(e1.elapsed_time(e2))
+        k6_bytes = st.numel() * 4 + Tb * H * W * 4          # every output element written once, every input frame read once
+        k6 = dict(nonempty_ms=float(np.mean(ne_ms)), gather_ms=float(np.mean(ga_ms)), frames_per_launch=int(fr.numel()),
+                  gather_gbs=k6_bytes / (float(np.mean(ga_ms)) * 1e-3) / 1e9, algorithmic_bytes=int(k6_bytes),
+                  note='gather_ms includes the torch.nonzero of the tile table')
+        del Xb, st
     alg = algorithmic_bytes(frame_dets, res.keys, H, W, MAX_PX)
     k2 = float(np.mean(k2ms)) * 1e-3
     peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
@@ -371,7 +395,7 @@ def run_b200(args, wl):
     roofline = dict(bound='hbm', kernel=klabel,
                     achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
                     peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
-                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)), k5_feature_hist_ms=float(np.mean(k5ms)),
+                    algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)), k5_feature_hist_ms=float(np.mean(k5ms)), k6_tiling=k6,
                     traffic=traffic)
 
     # ---- e2e: host buffers through the C ABI ------------------------------------------------------

@@ -193,6 +193,29 @@ int axb_feature_hist(axb_ctx* ctx, const float* image_dev, int H, int W,
                      const int32_t* boxes_dev, int n_boxes, int bins, float lo, float hi,
                      float* out_dev, void* stream);
 
+/* ---- tiling front end of the detector --------------------------------------
+ * X_dev float32 [T][C][H][W]: the dense timelapse (Timelapse.X.to_dense(), Timelapse.py:426-433:
+ * channel 0 image, 1 / 2 positive / negative motion), resident in HBM; tiles are tilesize x tilesize,
+ * ytiles = ceil(H / tilesize), xtiles = ceil(W / tilesize), zero padded at the right and bottom
+ * border (Timelapse.construct_tiles, Timelapse.py:508-525).
+ *
+ * axb_tile_nonempty replaces tile_info[..., 0] (Timelapse.py:551: (X[:, :, :, 0] > 0).any(-1).any(-1)):
+ * nonempty_dev uint8 [ytiles * xtiles][T].  The tiles the reference keeps are those with a flag set at
+ * any t (Timelapse.py:558), in row-major order -- the compact tile list tile_yx of axb_decode_nms.
+ *
+ * axb_gather_frametiles replaces Timelapse.get_frametiles_stack (Timelapse.py:150-157, __getitem__
+ * :111-125) for n_frames frames at once: out_dev float32
+ * [n_frames][ntiles][(2 * temporal_context + 1) * chan_n][tilesize][tilesize], plane
+ * (dt, ch) = X[frames_dev[b] + dt - temporal_context][chan_lo + ch] cut at tile tile_yx_dev[i] =
+ * (tile_y, tile_x).  USE_MOTION_DATA 'exclude' / 'temp_context' = channels (0, 1), 'only' = (1, 2),
+ * 'include' = (0, 3).  A frame whose temporal context leaves [0, T) sets AXB_ERR_BAD_ARG in axb_status
+ * (its planes are written as zeros). */
+int axb_tile_nonempty(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
+                      uint8_t* nonempty_dev, void* stream);
+int axb_gather_frametiles(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
+                          const int32_t* tile_yx_dev, int ntiles, const int32_t* frames_dev, int n_frames,
+                          int temporal_context, int chan_lo, int chan_n, float* out_dev, void* stream);
+
 /* ---- transition costs ------------------------------------------------------------------
  * Replaces the arithmetic of mincostflow_models.transition_model (mincostflow_models.py:100-119)
  * and the arc cost int(multi_factor * cost) of libmot's graph builder

@@ -318,3 +318,35 @@ def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
         shift = float(np.float32(0.0) - np.float32(smin * scale))
         out[i] = (cnt.astype(np.float64) * scale + shift).astype(np.float32)   # exact product + one rounding = fma
     return out
+
+
+MOTION_CHANNELS = {'exclude': (0, 1), 'temp_context': (0, 1), 'only': (1, 2), 'include': (0, 3)}
+
+
+def tile_frames(X, tilesize=512):
+    """The image half of Timelapse.construct_tiles (Timelapse.py:508-525, 539-558), numpy.
+    X float32 [T, C, H, W] -> (X_tiled [T, ntiles, C, ts, ts] of the tiles non-empty at any t, row-major;
+    nonempty bool [ytiles, xtiles, T] = tile_info[..., 0]; tile_yx int32 [ntiles, 2])."""
+    X = np.asarray(X, np.float32)
+    T, C, H, W = X.shape
+    ts = int(tilesize)
+    yt, xt = -(-H // ts), -(-W // ts)
+    pad = np.zeros((T, C, yt * ts, xt * ts), np.float32)          # ZeroPad2d right / bottom (:521-525)
+    pad[:, :, :H, :W] = X
+    tiles = pad.reshape(T, C, yt, ts, xt, ts).transpose(2, 4, 0, 1, 3, 5)   # ytile, xtile, t, c, y, x (:543)
+    nonempty = (tiles[:, :, :, 0] > 0).any(-1).any(-1)            # :550
+    keep = nonempty.any(-1)                                       # :558
+    X_tiled = tiles[keep].swapaxes(0, 1)
+    tile_yx = np.argwhere(keep).astype(np.int32)
+    return np.ascontiguousarray(X_tiled), nonempty, tile_yx
+
+
+def frametiles_stack(X_tiled, frame, temporal_context=2, use_motion_filtered='exclude'):
+    """Timelapse.get_frametiles_stack (Timelapse.py:150-157) over __getitem__ (:111-125) for the raw
+    frame index ``frame`` = timepoints_indices[t]: float32 [ntiles, (2tc+1)*nch, ts, ts]."""
+    lo, n = MOTION_CHANNELS[use_motion_filtered]
+    a, b = frame - temporal_context, frame + temporal_context + 1
+    assert a >= 0 and b <= X_tiled.shape[0], "a frame's temporal context leaves the timelapse"
+    st = X_tiled[a:b, :, lo:lo + n]                               # [2tc+1, ntiles, nch, ts, ts]
+    st = st.transpose(1, 0, 2, 3, 4)
+    return np.ascontiguousarray(st.reshape(st.shape[0], -1, *st.shape[3:]))
