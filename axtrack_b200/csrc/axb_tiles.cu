@@ -46,13 +46,15 @@ __global__ void __launch_bounds__(256) k6_gather_kernel(const float* __restrict_
     const int nst = 2 * tc + 1;
     const long long n_planes = (long long)B * ntiles * nst * nch;
     for (long long job = blockIdx.x; job < n_planes * chunks; job += gridDim.x) {
-        const long long plane = job / chunks;
-        const int chunk = (int)(job - plane * chunks);
-        long long q = plane;
-        const int ch = (int)(q % nch); q /= nch;
+        // job order: (tile, chunk, ch) major, (b, dt) minor -- the 2tc+1 readers of one source row block
+        // (neighbouring timepoints) run back to back, so HBM delivers every input row once and L2 the rest
+        long long q = job;
         const int dt = (int)(q % nst); q /= nst;
-        const int tile = (int)(q % ntiles);
-        const int b = (int)(q / ntiles);
+        const int b = (int)(q % B); q /= B;
+        const int ch = (int)(q % nch); q /= nch;
+        const int chunk = (int)(q % chunks);
+        const int tile = (int)(q / chunks);
+        const long long plane = (((long long)b * ntiles + tile) * nst + dt) * nch + ch;
         const int t = frames[b] + dt - tc;
         const bool bad = t < 0 || t >= T;                         // CTA-uniform
         if (bad && threadIdx.x == 0) atomicOr(err_flags, 16ull);

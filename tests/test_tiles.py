@@ -139,3 +139,59 @@ def test_frame_tiler_batches_the_forward():
     assert head.calls == [10, 10, 5] and tuple(Y.shape) == (5, 5, 2, 2, 3)
     one = torch.stack([head.detect_axons(tiler.get_frametiles_stack(t)) for t in range(len(tiler))])
     assert torch.equal(Y, one)
+
+
+@pytest.mark.gpu
+def test_drop_in_detect_dataset_with_frames_per_forward(tmp_path):
+    """detect_dataset() with the opt-in K6 front end (`frames_per_forward`) == the default path that tiles
+    through dataset.get_frametiles_stack, for a head that is a per-tile function of the pixels."""
+    import torch
+    from axtrack_b200.axon_detections import make_drop_in
+    from tests.test_gpu_dropin import _Base
+    rng = np.random.default_rng(21)
+    T, H, W, ts, tc = 8, 1000, 1400, 512, 2
+    X = np.zeros((T, 3, H, W), np.float32)
+    for t in range(T):                                     # sparse bright spots -> a few cells above threshold
+        yy, xx = rng.integers(0, H, 300), rng.integers(0, W, 300)
+        X[t, 0, yy, xx] = rng.random(300, dtype=np.float32) * 2000
+    X[:, 0, 512:, :512] = 0                                # an empty tile
+    X_tiled, nonempty, tile_yx = oracle.tile_frames(X, ts)
+
+    class DS:
+        name, sizet, sizey, sizex, tilesize, temporal_context = 'k6', T - 2 * tc, H, W, ts, tc
+        use_motion_filtered, timepoints_indices = 'exclude', list(range(tc, T - tc))
+        ytiles, xtiles = nonempty.shape[:2]
+        tile_info = torch.from_numpy(np.stack([nonempty, nonempty], -1))
+        target_tiled = torch.zeros((T, len(tile_yx), 12, 12, 4))
+
+        def __init__(self):
+            self.X = torch.from_numpy(X).to_sparse()
+
+        def construct_tiles(self, *a, **k):
+            pass
+
+        def get_frametiles_stack(self, t, device=None):
+            x = torch.from_numpy(oracle.frametiles_stack(X_tiled, self.timepoints_indices[t], tc, 'exclude'))
+            return x.to(device), self.target_tiled[self.timepoints_indices[t]].to(device)
+
+    class Model:
+        def detect_axons(self, Xb):                        # per-tile, batch-size independent
+            m = torch.nn.functional.adaptive_max_pool2d(Xb[:, tc:tc + 1], 12)[:, 0]          # [n, 12(y), 12(x)]
+            conf = (m / 2000).transpose(1, 2)
+            return torch.stack([conf, torch.full_like(conf, .5), torch.full_like(conf, .25)], -1)
+
+    def run(fpf):
+        ad = make_drop_in(_Base)(Model(), DS(), str(tmp_path))
+        ad.device = 'cuda'
+        ad.timepoint_subset = range(T - 2 * tc)
+        if fpf:
+            ad.frames_per_forward = fpf
+        ad.detect_dataset()
+        return ad
+
+    a, b = run(None), run(3)
+    assert sum(len(d) for d in a._detections) > 20
+    for da, db in zip(a._detections, b._detections):
+        assert da.equals(db)
+    for ta, tb in zip(a._yolo_targets, b._yolo_targets):
+        assert torch.equal(ta.cpu(), tb.cpu())
