@@ -7,7 +7,7 @@
 // X_tiled[t - tc : t + tc + 1, tile, channels].flatten(end_dim=1)), which the reference runs as a Python
 // loop over tiles per frame and one model forward per frame.  Here the timelapse X [T][C][H][W] stays
 // where it is in HBM (no X_tiled copy of the whole timelapse) and
-//   k6_nonempty_kernel  one CTA per (tile, frame): any(X[t][0][tile] > 0), early exit per 16 rows;
+//   k6_nonempty_kernel  CTAs per (tile, frame, 64-row band): any(X[t][0][tile] > 0), early exit per 8 rows;
 //   k6_gather_kernel    writes the model input of a BATCH of frames [B][ntiles][(2tc+1)*nch][ts][ts]
 //                       straight from X, zero filled outside the image: a pure copy, 4 B read + 4 B
 //                       written per element, float4 when the rows allow it.  Both are HBM bound.
@@ -15,25 +15,43 @@
 
 namespace axb {
 
+// flags are zeroed by the launcher; blockIdx.z = a band of kBandRows tile rows, so an empty 512x512 tile is
+// read by 8 CTAs instead of one.  A CTA that finds a positive pixel stores 1 (every writer stores the same
+// byte, no atomic needed) and leaves; a CTA whose flag is already set leaves at once.
+constexpr int kBandRows = 64;
+constexpr int kRoundRows = 8;      // rows between two early-exit checks
+template <bool VEC>
 __global__ void __launch_bounds__(256) k6_nonempty_kernel(const float* __restrict__ X, int T, int C, int H, int W, int ts,
                                                           int xtiles, uint8_t* __restrict__ nonempty) {
     const int tile = blockIdx.x, t = blockIdx.y;
     const int ty = tile / xtiles, tx = tile - ty * xtiles;
-    const int y0 = ty * ts, x0 = tx * ts;
-    const int h = min(ts, H - y0), w = min(ts, W - x0);
+    const int band = (int)blockIdx.z;                              // signed: H - y0 below may be negative
+    const int y0 = ty * ts + band * kBandRows, x0 = tx * ts;
+    const int h = min(min(kBandRows, ts - band * kBandRows), H - y0), w = min(ts, W - x0);
+    if (h <= 0) return;
     const float* const img = X + ((size_t)t * C) * H * W;          // channel 0 of frame t
-    int any = 0;
-    for (int r0 = 0; r0 < h; r0 += 16) {
-        const int rows = min(16, h - r0);
-        int mine = 0;
-        for (int i = threadIdx.x; i < rows * w; i += blockDim.x) {
-            const int r = i / w, c = i - r * w;
-            mine |= img[(size_t)(y0 + r0 + r) * W + x0 + c] > 0.0f;
+    volatile uint8_t* const flag = nonempty + (size_t)tile * T + t;
+    for (int r0 = 0; r0 < h; r0 += kRoundRows) {
+        const int rows = min(kRoundRows, h - r0);
+        int mine = *flag;
+        if (VEC) {                                                 // W % 4 == 0 and ts % 4 == 0: w % 4 == 0
+            const int wq = w >> 2;
+            for (int i = threadIdx.x; i < rows * wq; i += blockDim.x) {
+                const int r = i / wq, c = (i - r * wq) << 2;
+                const float4 v = __ldg(reinterpret_cast<const float4*>(img + (size_t)(y0 + r0 + r) * W + x0 + c));
+                mine |= (v.x > 0.0f) | (v.y > 0.0f) | (v.z > 0.0f) | (v.w > 0.0f);
+            }
+        } else {
+            for (int i = threadIdx.x; i < rows * w; i += blockDim.x) {
+                const int r = i / w, c = i - r * w;
+                mine |= __ldg(img + (size_t)(y0 + r0 + r) * W + x0 + c) > 0.0f;
+            }
         }
-        any = __syncthreads_or(mine);
-        if (any) break;
+        if (__syncthreads_or(mine)) {
+            if (threadIdx.x == 0) *flag = 1;
+            return;
+        }
     }
-    if (threadIdx.x == 0) nonempty[(size_t)tile * T + t] = (uint8_t)(any != 0);
 }
 
 template <bool VEC>
@@ -83,8 +101,11 @@ __global__ void __launch_bounds__(256) k6_gather_kernel(const float* __restrict_
 
 void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint8_t* nonempty, cudaStream_t stream) {
     const int ytiles = (H + ts - 1) / ts, xtiles = (W + ts - 1) / ts;
-    const dim3 grid((unsigned)(ytiles * xtiles), (unsigned)T);
-    k6_nonempty_kernel<<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, nonempty);
+    cudaMemsetAsync(nonempty, 0, (size_t)ytiles * xtiles * T, stream);
+    const dim3 grid((unsigned)(ytiles * xtiles), (unsigned)T, (unsigned)((ts + kBandRows - 1) / kBandRows));
+    const bool vec = (ts % 4 == 0) && (W % 4 == 0) && (reinterpret_cast<uintptr_t>(X) % 16 == 0);
+    if (vec) k6_nonempty_kernel<true><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, nonempty);
+    else k6_nonempty_kernel<false><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, nonempty);
 }
 
 void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,

@@ -67,7 +67,7 @@ def test_cuda_matches_reference_fixtures_and_oracle(golden_dir):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('H,W,ts', [(1000, 1030, 512), (1024, 1024, 512), (130, 67, 50), (37, 41, 512)])
+@pytest.mark.parametrize('H,W,ts', [(1000, 1030, 512), (1024, 1024, 512), (130, 67, 50), (37, 41, 512), (600, 520, 512), (200, 24, 128)])
 def test_cuda_matches_oracle_ragged(H, W, ts):
     """Vector path (W % 4 == 0) and scalar path, images smaller than a tile, ragged borders, NaN pixels."""
     import torch
