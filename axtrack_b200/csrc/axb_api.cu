@@ -42,6 +42,8 @@ struct axb_ctx {
     float* st_wc = nullptr;           size_t st_wc_bytes = 0;
     // staging for axb_decode_nms_host: one arena
     uint8_t* st_k1 = nullptr;         size_t st_k1_bytes = 0;
+    // K6: one flag word per 32-byte sector while the bands of a tile vote
+    uint32_t* k6_flags = nullptr;     size_t k6_flags_bytes = 0;
 };
 
 namespace {
@@ -125,7 +127,7 @@ void axb_destroy(axb_ctx* c) {
     cudaFree(c->trace_par); cudaFree(c->trace_iota); cudaFree(c->k2_wide_scratch); cudaFree(c->trace_par_wide);
     cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
-    cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1);
+    cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1); cudaFree(c->k6_flags);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -474,8 +476,11 @@ int axb_tile_nonempty(axb_ctx* c, const float* X_dev, int T, int C, int H, int W
     if (T == 0) return AXB_OK;
     if (!X_dev || !nonempty_dev) return bad_arg(c, "axb_tile_nonempty: NULL pointer");
     AXB_CUDA(c, cudaSetDevice(c->device));
-    axb::launch_k6_nonempty(X_dev, T, C, H, W, tilesize, nonempty_dev, (cudaStream_t)stream);
-    c->launches += 1;
+    const size_t n_flags = (size_t)((H + tilesize - 1) / tilesize) * ((W + tilesize - 1) / tilesize) * T;
+    int rc = grow(c, &c->k6_flags, &c->k6_flags_bytes, n_flags * axb::kK6FlagStride * sizeof(uint32_t));
+    if (rc != AXB_OK) return rc;
+    axb::launch_k6_nonempty(X_dev, T, C, H, W, tilesize, c->k6_flags, nonempty_dev, (cudaStream_t)stream);
+    c->launches += 2;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;
 }

@@ -125,7 +125,8 @@ void launch_k3(const int32_t* path_len, const axb_pair_desc* pairs, int n_pairs,
 void launch_k5(const float* image, int H, int W, const int32_t* boxes, int n_boxes, int bins, float lo, float hi,
                float* out, cudaStream_t stream);
 
-void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint8_t* nonempty, cudaStream_t stream);
+constexpr int kK6FlagStride = 8;      // uint32 words between two K6 vote flags: one flag per 32-byte sector
+void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint32_t* flags, uint8_t* nonempty, cudaStream_t stream);
 void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,
                       const int32_t* frames, int B, int tc, int chan_lo, int nch, float* out,
                       unsigned long long* err_flags, int n_sms, cudaStream_t stream);

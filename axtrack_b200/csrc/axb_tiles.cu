@@ -17,12 +17,14 @@ namespace axb {
 
 // flags are zeroed by the launcher; blockIdx.z = a band of kBandRows tile rows, so an empty 512x512 tile is
 // read by 8 CTAs instead of one.  A CTA that finds a positive pixel stores 1 (every writer stores the same
-// byte, no atomic needed) and leaves; a CTA whose flag is already set leaves at once.
+// word, no atomic needed) and leaves; a CTA whose flag is already set leaves at once.  The vote flags sit
+// one per 32-byte sector (kK6FlagStride words apart): packed bytes made the stores of all bands of 32
+// (tile, frame) neighbours serialise on one L2 sector; k6_flags_to_bytes_kernel packs them afterwards.
 constexpr int kBandRows = 64;
 constexpr int kRoundRows = 8;      // rows between two early-exit checks
 template <bool VEC>
 __global__ void __launch_bounds__(256) k6_nonempty_kernel(const float* __restrict__ X, int T, int C, int H, int W, int ts,
-                                                          int xtiles, uint8_t* __restrict__ nonempty) {
+                                                          int xtiles, uint32_t* __restrict__ flags) {
     const int tile = blockIdx.x, t = blockIdx.y;
     const int ty = tile / xtiles, tx = tile - ty * xtiles;
     const int band = (int)blockIdx.z;                              // signed: H - y0 below may be negative
@@ -30,10 +32,10 @@ __global__ void __launch_bounds__(256) k6_nonempty_kernel(const float* __restric
     const int h = min(min(kBandRows, ts - band * kBandRows), H - y0), w = min(ts, W - x0);
     if (h <= 0) return;
     const float* const img = X + ((size_t)t * C) * H * W;          // channel 0 of frame t
-    volatile uint8_t* const flag = nonempty + (size_t)tile * T + t;
+    volatile uint32_t* const flag = flags + ((size_t)tile * T + t) * kK6FlagStride;
     for (int r0 = 0; r0 < h; r0 += kRoundRows) {
         const int rows = min(kRoundRows, h - r0);
-        int mine = *flag;
+        int mine = (int)*flag;
         if (VEC) {                                                 // W % 4 == 0 and ts % 4 == 0: w % 4 == 0
             const int wq = w >> 2;
             for (int i = threadIdx.x; i < rows * wq; i += blockDim.x) {
@@ -48,10 +50,15 @@ __global__ void __launch_bounds__(256) k6_nonempty_kernel(const float* __restric
             }
         }
         if (__syncthreads_or(mine)) {
-            if (threadIdx.x == 0) *flag = 1;
+            if (threadIdx.x == 0 && *flag == 0) *flag = 1;
             return;
         }
     }
+}
+
+__global__ void __launch_bounds__(256) k6_flags_to_bytes_kernel(const uint32_t* __restrict__ flags, size_t n, uint8_t* __restrict__ nonempty) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) nonempty[i] = (uint8_t)(flags[i * kK6FlagStride] != 0);
 }
 
 template <bool VEC>
@@ -99,13 +106,15 @@ __global__ void __launch_bounds__(256) k6_gather_kernel(const float* __restrict_
     }
 }
 
-void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint8_t* nonempty, cudaStream_t stream) {
+void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint32_t* flags, uint8_t* nonempty, cudaStream_t stream) {
     const int ytiles = (H + ts - 1) / ts, xtiles = (W + ts - 1) / ts;
-    cudaMemsetAsync(nonempty, 0, (size_t)ytiles * xtiles * T, stream);
+    const size_t n = (size_t)ytiles * xtiles * T;
+    cudaMemsetAsync(flags, 0, n * kK6FlagStride * sizeof(uint32_t), stream);
     const dim3 grid((unsigned)(ytiles * xtiles), (unsigned)T, (unsigned)((ts + kBandRows - 1) / kBandRows));
     const bool vec = (ts % 4 == 0) && (W % 4 == 0) && (reinterpret_cast<uintptr_t>(X) % 16 == 0);
-    if (vec) k6_nonempty_kernel<true><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, nonempty);
-    else k6_nonempty_kernel<false><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, nonempty);
+    if (vec) k6_nonempty_kernel<true><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, flags);
+    else k6_nonempty_kernel<false><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, flags);
+    k6_flags_to_bytes_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(flags, n, nonempty);
 }
 
 void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,
