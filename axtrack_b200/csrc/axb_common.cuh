@@ -29,7 +29,10 @@ constexpr int kSeedCalWide = 1024;
 constexpr int kFastMaxPx = 511;       // largest radius of the 1024-column folded window (tile-word kernels, shared-memory bitmaps)
 static_assert(AXB_MAX_PX == 1023, "wide layout: 2048-bit folded rows");
 // fast kernel (level 0 only): 3 CTAs per SM
-constexpr int kFastThreads = 96;      // fast kernels: one CTA (3 warps) per source search, one thread per frontier entry
+#ifndef AXB_FAST_THREADS
+#define AXB_FAST_THREADS 96
+#endif
+constexpr int kFastThreads = AXB_FAST_THREADS;      // fast kernels: one CTA (3 warps) per source search, one thread per frontier entry
 constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entries per buffer
 // dense window (every tile word of the folded diamond, 64.5 KB): 3 CTAs per SM
 constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory

@@ -151,20 +151,36 @@ def assemble(gathered, blocks, max_num_misses=1):
     return res
 
 
-def associate_sharded(Y, tile_yx, mask, max_px=500, max_num_misses=1, group=None, slabs=None, **kw):
+def block_inputs(block, Y, mask_of_frame=None):
+    """What one rank feeds to ``associate_frames`` for its ``partition`` block: the head tensors of its
+    frames (halo included) and -- with per-frame masks -- the slice of ``mask_of_frame`` that belongs to
+    them.  ``build_pairs`` indexes ``mask_of_frame`` with the block-LOCAL frame index, so the global
+    table must be cut exactly like Y."""
+    first, own, stop = block
+    mof = None if mask_of_frame is None else np.asarray(mask_of_frame)[first:stop]
+    return Y[first:stop], own - first, mof
+
+
+def associate_block(block, Y, tile_yx, mask, max_px=500, max_num_misses=1, mask_of_frame=None, out_alloc=None, **kw):
+    """The association path of one timepoint block (``partition``) on the current GPU."""
+    from . import pipeline
+    Yb, t0, mof = block_inputs(block, Y, mask_of_frame)
+    return pipeline.associate_frames(Yb, tile_yx, mask, max_px=max_px, max_num_misses=max_num_misses, t0=t0,
+                                     want_cost=False, mask_of_frame=mof, out_alloc=out_alloc, **kw)
+
+
+def associate_sharded(Y, tile_yx, mask, max_px=500, max_num_misses=1, group=None, slabs=None, mask_of_frame=None, **kw):
     """Each rank passes the WHOLE head tensor Y [T, ...] (or at least its own block + halo rows at
     their global positions) and processes its block on its own GPU; rank 0 gets the assembled dict.
+    ``mask_of_frame`` [T] (global frame -> mask index) goes with per-frame masks [n_masks, H, W].
     ``slabs`` (a PeerSlabs, CUDA + NCCL): the kernels write into rank 0's memory directly; without
     it the matrices are gathered with NCCL / gloo sends after the kernels."""
-    from . import pipeline
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     T = Y.shape[0]
     blocks = partition(T, world, max_num_misses)
-    first, own, stop = blocks[rank]
-    res = pipeline.associate_frames(Y[first:stop], tile_yx, mask, max_px=max_px, max_num_misses=max_num_misses,
-                                    t0=own - first, want_cost=False,
-                                    out_alloc=slabs.out_alloc if slabs is not None else None, **kw)
+    res = associate_block(blocks[rank], Y, tile_yx, mask, max_px, max_num_misses, mask_of_frame,
+                          out_alloc=slabs.out_alloc if slabs is not None else None, **kw)
     shapes = torch.from_numpy(np.stack([res.pairs['n_src'], res.pairs['n_dst']], 1).astype(np.int64).reshape(-1, 2))
     if slabs is not None:
         slabs.publish(res.path_len.numel(), shapes)

@@ -69,6 +69,9 @@ def lib():
             fn.restype = c_int
             fn.argtypes = [u8p, c_int, c_int, i32p, c_int, i32p, c_int, c_int,
                            i32p, u8p, f32p, ctypes.POINTER(ctypes.c_int64)]
+        L.axo_cost_matrix_rule_ex.restype = c_int
+        L.axo_cost_matrix_rule_ex.argtypes = [u8p, c_int, c_int, i32p, c_int, i32p, c_int, c_int,
+                                              i32p, u8p, f32p, ctypes.POINTER(ctypes.c_int64), u8p]
         _LIB = L
     return _LIB
 
@@ -138,6 +141,21 @@ def cost_matrix_astar(mask, src_yx, dst_yx, max_px=500):
 def cost_matrix_rule(mask, src_yx, dst_yx, max_px=500):
     """Closed form (one bounded search per source).  Same outputs as cost_matrix_astar."""
     return _cost_matrix(lib().axo_cost_matrix_rule, mask, src_yx, dst_yx, max_px)
+
+
+def cost_matrix_rule_ex(mask, src_yx, dst_yx, max_px=500):
+    """cost_matrix_rule plus ``tie_regime`` uint8 [n_src, n_dst]: 1 where the reference's answer depends
+    on the pop order of equal-priority heap entries (see astar_oracle.cpp); the rule is exact elsewhere."""
+    mask, src, dst, pl, un, wc = _prep(mask, src_yx, dst_yx)
+    tie = np.zeros(pl.shape[0], np.uint8)
+    err = ctypes.c_int64(-1)
+    rc = lib().axo_cost_matrix_rule_ex(mask.reshape(-1), mask.shape[0], mask.shape[1], src.reshape(-1), src.shape[0],
+                                       dst.reshape(-1), dst.shape[0], int(max_px), pl, un, wc, ctypes.byref(err), tie)
+    if rc != 0:
+        _raise(rc, err.value, src, dst)
+    shp = (src.shape[0], dst.shape[0])
+    k = shp[0] * shp[1]
+    return pl[:k].reshape(shp), un[:k].reshape(shp), wc[:k].reshape(shp), tie[:k].reshape(shp)
 
 
 # ----------------------------------------------------------------------------------------

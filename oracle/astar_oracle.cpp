@@ -192,10 +192,18 @@ int axo_cost_matrix_astar(const uint8_t* mask, int H, int W,
 //     L = k_T + j_T + 1 if  L <= max_px  and  k_T <= k*   else None
 // because an entry at hop max_px of a lower level always has a smaller A* priority than the
 // goal (65536 >> 2*max_px) and is therefore popped -- and triggers the cut-off -- first.
-int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
+//
+// tie_regime (optional, [n_src*n_dst]): 1 where the reference's answer is decided by the pop order of
+// equal-priority heap entries (libstdc++ std::priority_queue), which no closed form reproduces: the
+// target sits in a level k_T >= 1 and some lower level k expanded cells at hop max_px-1 without
+// reaching hop max_px.  Such a cell can push an already-better-known neighbour with path_length
+// max_px+1 when it is expanded before that neighbour's own parent -- possible only on an exact
+// f-tie (DESIGN.md "Heap-tie corner") -- and that stale entry then triggers the cut-off
+// (astar.cpp:88-92) ahead of any goal of a higher level.  Everywhere else the rule is exact.
+static int cost_matrix_rule_impl(const uint8_t* mask, int H, int W,
                          const int32_t* src_yx, int n_src, const int32_t* dst_yx, int n_dst,
                          int max_px, int32_t* path_len, uint8_t* unreachable, float* wcost,
-                         int64_t* err_pair) {
+                         int64_t* err_pair, uint8_t* tie_regime) {
     const int64_t r2 = (int64_t)max_px * max_px;
     const int R = max_px;                 // cells at hop <= R are looked at
     const int side = 2 * R + 1;
@@ -210,6 +218,7 @@ int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
         for (int j = 0; j < n_dst; ++j) {
             const size_t o = (size_t)i * n_dst + j;
             path_len[o] = max_px; unreachable[o] = 1;
+            if (tie_regime) tie_regime[o] = 0;
             if (wcost) wcost[o] = std::numeric_limits<float>::infinity();
             const int ty = dst_yx[2 * j], tx = dst_yx[2 * j + 1];
             const int64_t dy = (int64_t)sy - ty, dx = (int64_t)sx - tx;
@@ -228,12 +237,13 @@ int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
         seeds.push_back({0, wl(sy, sx)});
         lev[wl(sy, sx)] = 0; fgc[wl(sy, sx)] = 0;
         int kstar = -1;
+        int ktie = -1;                     // first level that expanded hop max_px-1 without reaching hop max_px
         for (int k = 0; k <= R && kstar < 0 && !seeds.empty(); ++k) {
             // seeds are already settled (level k, their j); sorted by j by construction
             size_t sp = 0;
             cur.clear();
             int j = seeds[0].first;
-            bool hit_limit = false;
+            bool hit_limit = false, at_rm1 = false;
             while (true) {
                 while (sp < seeds.size() && seeds[sp].first == j) cur.push_back(seeds[sp++].second);
                 if (cur.empty()) {
@@ -245,6 +255,7 @@ int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
                     cur.clear();
                     if (sp >= seeds.size()) break;
                     j = seeds[sp].first; continue; }
+                if (hop == R - 1) at_rm1 = true;
                 nxt.clear();
                 for (int c : cur) {
                     const int y = c / side - R + sy, x = c % side - R + sx;
@@ -264,6 +275,7 @@ int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
                 ++j;
             }
             if (hit_limit) kstar = k;
+            else if (at_rm1 && ktie < 0) ktie = k;
             seeds.swap(seeds_next); seeds_next.clear();
         }
         for (int j = 0; j < n_dst; ++j) {
@@ -279,9 +291,24 @@ int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
             if (k + jj + 1 > max_px) continue;
             path_len[o] = k + jj + 1; unreachable[o] = 0;
             if (wcost) wcost[o] = (float)((double)k * 65536.0 + (double)jj);
+            if (tie_regime && ktie >= 0 && k > ktie) tie_regime[o] = 1;
         }
     }
     return 0;
+}
+
+int axo_cost_matrix_rule(const uint8_t* mask, int H, int W,
+                         const int32_t* src_yx, int n_src, const int32_t* dst_yx, int n_dst,
+                         int max_px, int32_t* path_len, uint8_t* unreachable, float* wcost,
+                         int64_t* err_pair) {
+    return cost_matrix_rule_impl(mask, H, W, src_yx, n_src, dst_yx, n_dst, max_px, path_len, unreachable, wcost, err_pair, nullptr);
+}
+
+int axo_cost_matrix_rule_ex(const uint8_t* mask, int H, int W,
+                            const int32_t* src_yx, int n_src, const int32_t* dst_yx, int n_dst,
+                            int max_px, int32_t* path_len, uint8_t* unreachable, float* wcost,
+                            int64_t* err_pair, uint8_t* tie_regime) {
+    return cost_matrix_rule_impl(mask, H, W, src_yx, n_src, dst_yx, n_dst, max_px, path_len, unreachable, wcost, err_pair, tie_regime);
 }
 
 }  // extern "C"

@@ -106,36 +106,82 @@ def test_compiled_reference_kat():
 
 
 # ---- closed form vs per-pair restatement --------------------------------------------------------------
-def test_rule_equals_astar_random():
-    rng = np.random.default_rng(11)
-    tot = bad = 0
-    for it in range(300):
-        H, W = int(rng.integers(20, 140)), int(rng.integers(20, 140))
-        m = np.zeros((H, W), bool)
-        for _ in range(int(rng.integers(2, 7))):
-            y = int(rng.integers(0, H)); w_ = int(rng.integers(1, 6)); m[y:y + w_, :] = True
-            x = int(rng.integers(0, W)); w_ = int(rng.integers(1, 6)); m[:, x:x + w_] = True
-        for _ in range(int(rng.integers(0, 8))):
-            y, x, g = int(rng.integers(0, H)), int(rng.integers(0, W)), int(rng.integers(1, 5))
-            m[y:y + g, x:x + g] = False
-        max_px = int(rng.choice([12, 25, 40, 80, 150]))
-        fg = np.argwhere(m)
+def _adversarial_case(rng):
+    H, W = int(rng.integers(20, 140)), int(rng.integers(20, 140))
+    m = np.zeros((H, W), bool)
+    for _ in range(int(rng.integers(2, 7))):
+        y = int(rng.integers(0, H)); w_ = int(rng.integers(1, 6)); m[y:y + w_, :] = True
+        x = int(rng.integers(0, W)); w_ = int(rng.integers(1, 6)); m[:, x:x + w_] = True
+    for _ in range(int(rng.integers(0, 8))):
+        y, x, g = int(rng.integers(0, H)), int(rng.integers(0, W)), int(rng.integers(1, 5))
+        m[y:y + g, x:x + g] = False
+    max_px = int(rng.choice([12, 25, 40, 80, 150]))
+    fg = np.argwhere(m)
 
-        def pick(n):
-            p = fg[rng.integers(0, len(fg), n)] + rng.integers(-2, 3, (n, 2)) * (rng.random((n, 1)) < 0.3)
-            p[:, 0] = np.clip(p[:, 0], 0, H - 1)
-            p[:, 1] = np.clip(p[:, 1], 0, W - 1)
-            return p
-        src, dst = pick(5), pick(9)
+    def pick(n):
+        p = fg[rng.integers(0, len(fg), n)] + rng.integers(-2, 3, (n, 2)) * (rng.random((n, 1)) < 0.3)
+        p[:, 0] = np.clip(p[:, 0], 0, H - 1)
+        p[:, 1] = np.clip(p[:, 1], 0, W - 1)
+        return p
+    return m, pick(5), pick(9), max_px
+
+
+def test_rule_equals_astar_random():
+    """The closed form against the restated per-pair A* on adversarial small grids: EXACT on every
+    pair outside the heap-tie regime (``tie_regime`` of cost_matrix_rule_ex: the reference's answer
+    there depends on the pop order of equal-priority std::priority_queue entries, DESIGN.md section 2);
+    a 6.4 M-pair sweep of this generator family found 49 differing pairs, all of them flagged
+    (tests/golden/make_heap_tie_cases.py)."""
+    rng = np.random.default_rng(11)
+    tot = flagged = 0
+    for it in range(300):
+        m, src, dst, max_px = _adversarial_case(rng)
         a = oracle.cost_matrix_astar(m, src, dst, max_px)
-        r = oracle.cost_matrix_rule(m, src, dst, max_px)
+        r = oracle.cost_matrix_rule_ex(m, src, dst, max_px)
+        clear = r[3] == 0
+        assert np.array_equal(a[0][clear], r[0][clear]) and np.array_equal(a[1][clear], r[1][clear]), it
         tot += a[0].size
-        bad += int(((a[0] != r[0]) | (a[1] != r[1])).sum())
+        flagged += int(r[3].sum())
         ok = (a[1] == 0) & (r[1] == 0) & (a[2] < 2 ** 24)
         assert np.array_equal(a[2][ok], r[2][ok])
-    # the closed form is exact except for the heap-tie corner documented in DESIGN.md
-    # ("a level whose deepest cell sits at hop max_px-1"): < 1e-4 of adversarial small-grid pairs
-    assert bad <= max(1, tot // 10000), (bad, tot)
+    assert tot == 300 * 45 and flagged < tot // 50, (flagged, tot)      # the regime stays a corner
+
+
+@pytest.mark.skipif(not oracle.ref_available(), reason='oracle/_ref not built')
+def test_rule_equals_compiled_reference_random():
+    """Same family against the COMPILED reference (oracle/_ref, astar.cpp unmodified)."""
+    rng = np.random.default_rng(12)
+    n = 0
+    for it in range(60):
+        m, src, dst, max_px = _adversarial_case(rng)
+        pl, un = oracle.ref_cost_matrix(m, src, dst, max_px, threads=False)
+        r = oracle.cost_matrix_rule_ex(m, src, dst, max_px)
+        clear = r[3] == 0
+        assert np.array_equal(pl[clear], r[0][clear]) and np.array_equal(un[clear], r[1][clear]), it
+        n += int(clear.sum())
+    assert n > 2500
+
+
+def test_heap_tie_fixture(golden_dir):
+    """The concrete counter-examples: pairs where the reference returns None
+    because a stale heap entry with path_length max_px+1 pops on an f-tie, while the closed form
+    finds the target.  The fixture holds the COMPILED reference's answers; the restated A* (same
+    std::priority_queue) reproduces them, the closed form flags every one of them as tie regime."""
+    g = np.load(os.path.join(golden_dir, 'heap_tie_cases.npz'))
+    n = int(g['n'])
+    assert n >= 12
+    for i in range(n):
+        H, W = g[f'shape_{i}']
+        m = np.unpackbits(g[f'mask_{i}'])[:H * W].reshape(H, W)
+        src, dst, max_px = g[f'src_{i}'][None], g[f'dst_{i}'][None], int(g[f'max_px_{i}'])
+        a = oracle.cost_matrix_astar(m, src, dst, max_px)
+        assert (int(a[0][0, 0]), int(a[1][0, 0])) == tuple(int(v) for v in g[f'ref_{i}']), i
+        r = oracle.cost_matrix_rule_ex(m, src, dst, max_px)
+        assert (int(r[0][0, 0]), int(r[1][0, 0])) == tuple(int(v) for v in g[f'rule_{i}']), i
+        assert r[3][0, 0] == 1 and g[f'ref_{i}'][1] == 1 and r[1][0, 0] == 0, i
+        if oracle.ref_available():
+            pl, un = oracle.ref_cost_matrix(m, src, dst, max_px, threads=False)
+            assert (int(pl[0, 0]), int(un[0, 0])) == tuple(int(v) for v in g[f'ref_{i}']), i
 
 
 # ---- fixtures generated from the unmodified reference ---------------------------------------------------

@@ -41,12 +41,17 @@ def _worker(rank, world, port, T, out_path):
     dist.init_process_group('gloo', rank=rank, world_size=world)
     try:
         mask = synth.make_mask(200, 240, 4, pitch=(40, 80), width=(4, 9))
+        masks = [mask, synth.make_mask(200, 240, 9, pitch=(40, 80), width=(4, 9))]     # per-frame masks
+        mask_of_frame = np.array([(t // 2) % 2 for t in range(T)])
         tracks = synth.make_tracks(mask, 12, T, 4, off_mask_frac=0.2)
         tracks[2] = np.zeros((0, 2), np.int32)          # an empty frame
         blocks = sharding.partition(T, world, 1)
+        first = blocks[rank][0]
+        _, t0, mof = sharding.block_inputs(blocks[rank], np.arange(T), mask_of_frame)    # what the rank's kernels get
+        assert t0 == blocks[rank][1] - first
         pls, uns, shapes = [], [], []
         for t, tb in sharding.global_keys(blocks[rank], 1):
-            pl, un, _ = oracle.cost_matrix_rule(mask, tracks[tb], tracks[t], 60)
+            pl, un, _ = oracle.cost_matrix_rule(masks[mof[t - first]], tracks[tb], tracks[t], 60)   # block-local index, as build_pairs
             pls.append(pl.reshape(-1)); uns.append(un.reshape(-1)); shapes.append((len(tracks[tb]), len(tracks[t])))
         cat = lambda xs, dt: torch.from_numpy(np.concatenate(xs).astype(dt)) if xs else torch.zeros(0, dtype=torch.from_numpy(np.zeros(0, dt)).dtype)
         g = sharding.gather_to_rank0(cat(pls, np.int32), cat(uns, np.uint8),
@@ -55,7 +60,7 @@ def _worker(rank, world, port, T, out_path):
             res = sharding.assemble(g, blocks, 1)
             assert list(res) == frame_pair_keys(T, 1)
             for (t, tb), (pl, un) in res.items():
-                rpl, run, _ = oracle.cost_matrix_rule(mask, tracks[tb], tracks[t], 60)
+                rpl, run, _ = oracle.cost_matrix_rule(masks[mask_of_frame[t]], tracks[tb], tracks[t], 60)   # the frame's own mask (AxonDetections.py:557)
                 assert np.array_equal(pl, rpl) and np.array_equal(un, run), (t, tb)
             open(out_path, 'w').write('ok %d' % len(res))
         else:
@@ -70,6 +75,50 @@ def test_gather_gloo(world, tmp_path):
     T = 7
     mp.spawn(_worker, args=(world, _free_port(), T, out), nprocs=world, join=True)
     assert open(out).read() == 'ok %d' % len(frame_pair_keys(T, 1))
+
+
+def test_block_inputs_cut_the_mask_table_like_the_frames():
+    T = 11
+    Y = np.arange(T)
+    mof = np.arange(T) % 3
+    for world in (1, 2, 3, 4):
+        for block in sharding.partition(T, world, 1):
+            Yb, t0, m = sharding.block_inputs(block, Y, mof)
+            assert len(Yb) == len(m) == block[2] - block[0] and t0 == block[1] - block[0]
+            assert np.array_equal(m, mof[Yb])              # local frame l is global frame Yb[l]
+            assert sharding.block_inputs(block, Y, None)[2] is None
+
+
+@pytest.mark.gpu
+def test_sharded_blocks_with_per_frame_masks():
+    """Every rank's block of a timelapse with TWO masks (per-frame mask table) on one GPU, assembled as
+    rank 0 does, against the unsharded result (the table must be cut like the frames)."""
+    if not torch.cuda.is_available():
+        pytest.fail('-m gpu tests need a CUDA device')
+    from axtrack_b200 import pipeline
+    dev = torch.device('cuda', 0)
+    H, W, T = 600, 700, 9
+    masks = np.stack([synth.make_mask(H, W, seed=3), synth.make_mask(H, W, seed=8)]).astype(np.uint8)
+    mof = np.array([0, 0, 1, 1, 1, 0, 1, 0, 0], np.int32)
+    tt = synth.tile_table(H, W)
+    rng = np.random.default_rng(5)
+    fg = np.argwhere(masks[0] & masks[1])
+    Y = np.stack([synth.make_head_tensor(fg[rng.integers(0, len(fg), 50)], H, W, seed=20 + t)[0] for t in range(T)])
+    Yd, td, md = torch.from_numpy(Y).to(dev), torch.from_numpy(tt).to(dev), torch.from_numpy(masks).to(dev)
+    ref = pipeline.associate_frames(Yd, td, md, want_cost=False, mask_of_frame=mof).pair_matrices()
+    one = pipeline.associate_frames(Yd, td, md[:1], want_cost=False).pair_matrices()
+    assert any(not np.array_equal(ref[k][0], one[k][0]) for k in ref), 'the two masks must matter'
+    for world in (2, 3):
+        blocks = sharding.partition(T, world, 1)
+        g = []
+        for b in blocks:
+            r = sharding.associate_block(b, Yd, td, md, mask_of_frame=mof)
+            g.append((r.path_len, r.unreachable,
+                      torch.from_numpy(np.stack([r.pairs['n_src'], r.pairs['n_dst']], 1).astype(np.int64).reshape(-1, 2))))
+        got = sharding.assemble(g, blocks, 1)
+        assert list(got) == list(ref)
+        for k in ref:
+            assert np.array_equal(got[k][0], ref[k][0]) and np.array_equal(got[k][1], ref[k][1]), (world, k)
 
 
 def _peer_worker(rank, world, port, out_path):
@@ -106,7 +155,7 @@ def _peer_worker(rank, world, port, out_path):
 @pytest.mark.gpu
 def test_peer_slabs_single_rank(tmp_path):
     """The N > 1 product path (kernels store into rank 0's symmetric-memory slab) with world_size 1
-    on one GPU; the 2- and 8-GPU runs are scratch/peer_check.py and bench.py --gpus N."""
+    on one GPU; the 2- and 8-GPU runs are tools/peer_check.py and bench.py --gpus N."""
     if not torch.cuda.is_available():
         pytest.fail('-m gpu tests need a CUDA device')
     out = str(tmp_path / 'ok.txt')
