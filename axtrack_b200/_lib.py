@@ -70,7 +70,7 @@ def load():
     L.axb_pack_weights.restype = ci
     L.axb_pack_weights.argtypes = [vp, vp, ci, ci, ci, vp, vp]
     L.axb_cost_matrix_batch.restype = ci
-    L.axb_cost_matrix_batch.argtypes = [vp, vp, ci, ci, ci, vp, vp, ci, ci, ci, vp, vp, vp, vp]
+    L.axb_cost_matrix_batch.argtypes = [vp, vp, ci, ci, ci, vp, ci, vp, ci, ci, ci, vp, vp, vp, ctypes.c_int64, vp]
     L.axb_cost_matrix.restype = ci
     L.axb_cost_matrix.argtypes = [vp, vp, ci, ci, vp, ci, vp, ci, ci, vp, vp, vp, vp]
     L.axb_cost_matrix_batch_host.restype = ci

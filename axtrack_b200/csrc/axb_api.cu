@@ -59,6 +59,19 @@ bool cuda_ok(axb_ctx* c, cudaError_t e, const char* what) {
 
 int bad_arg(axb_ctx* c, const char* msg) { if (c) c->err = msg; return AXB_ERR_BAD_ARG; }
 
+// Every entry point runs on the ctx's device and leaves the calling thread's current device as it
+// found it (the caller may be a framework that tracks its own current device).
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) err = cudaSetDevice(dev); else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define AXB_ON_DEVICE(c) DeviceGuard axb_guard_((c)->device); AXB_CUDA((c), axb_guard_.err)
+
 template <class T>
 int grow(axb_ctx* c, T** ptr, size_t* have, size_t need) {
     if (need <= *have && *ptr) return AXB_OK;
@@ -140,7 +153,7 @@ int axb_pack_mask(axb_ctx* c, const uint8_t* mask_dev, int n_masks, int H, int W
                   uint32_t* mask_bits_dev, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (!mask_dev || !mask_bits_dev || n_masks < 0 || H <= 0 || W <= 0) return bad_arg(c, "axb_pack_mask: bad argument");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     axb::launch_pack_mask_u8(mask_dev, n_masks, H, W, mask_bits_dev, (cudaStream_t)stream);
     c->launches += 1;
     AXB_CUDA(c, cudaGetLastError());
@@ -151,7 +164,7 @@ int axb_pack_weights(axb_ctx* c, const float* weights_dev, int n_masks, int H, i
                      uint32_t* mask_bits_dev, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (!weights_dev || !mask_bits_dev || n_masks < 0 || H <= 0 || W <= 0) return bad_arg(c, "axb_pack_weights: bad argument");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     axb::launch_pack_mask_f32(weights_dev, n_masks, H, W, mask_bits_dev, c->status_dev + 1, (cudaStream_t)stream);
     c->launches += 1;
     AXB_CUDA(c, cudaGetLastError());
@@ -159,16 +172,18 @@ int axb_pack_weights(axb_ctx* c, const float* weights_dev, int n_masks, int H, i
 }
 
 int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
-                          const int32_t* dets_yx_dev, const axb_pair_desc* pairs_dev, int n_pairs,
+                          const int32_t* dets_yx_dev, int n_dets, const axb_pair_desc* pairs_dev, int n_pairs,
                           int total_src, int max_px,
-                          int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, void* stream) {
+                          int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, int64_t out_capacity,
+                          void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
-    if (n_pairs < 0 || total_src < 0 || H <= 0 || W <= 0 || n_masks <= 0) return bad_arg(c, "axb_cost_matrix_batch: bad size");
+    if (n_pairs < 0 || total_src < 0 || H <= 0 || W <= 0 || n_masks <= 0 || n_dets < 0 || out_capacity < 0)
+        return bad_arg(c, "axb_cost_matrix_batch: bad size");
     if (max_px < 1 || max_px > AXB_MAX_PX) return bad_arg(c, "axb_cost_matrix_batch: max_px outside [1, AXB_MAX_PX]");
     if (n_pairs == 0 || total_src == 0) return AXB_OK;
     if (!mask_bits_dev || !dets_yx_dev || !pairs_dev || !path_len_dev || !unreachable_dev)
         return bad_arg(c, "axb_cost_matrix_batch: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     cudaStream_t s = (cudaStream_t)stream;
     int rc = ensure_k2(c, n_pairs, total_src);
     if (rc != AXB_OK) return rc;
@@ -182,7 +197,8 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     int* const work_prefix = c->prefix_dev;
     int* const all_prefix = c->prefix_dev + c->prefix_cap;
     int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
-    axb::launch_k2_prep(pairs_dev, n_pairs, work_prefix, all_prefix, next_same, c->counters, s);
+    axb::launch_k2_prep(pairs_dev, n_pairs, work_prefix, all_prefix, next_same, c->counters, n_masks, n_dets,
+                        (long long)out_capacity, total_src, c->status_dev + 1, s);
     c->last_n_pairs = n_pairs;
     axb::K2Params p;
     p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = Wp;
@@ -216,7 +232,7 @@ int axb_cost_matrix(axb_ctx* c, const uint32_t* mask_bits_dev, int H, int W,
     if (n_src < 0 || n_dst < 0) return bad_arg(c, "axb_cost_matrix: negative count");
     if (n_src == 0 || n_dst == 0) return AXB_OK;
     if (!src_yx_dev || !dst_yx_dev) return bad_arg(c, "axb_cost_matrix: NULL detections");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     cudaStream_t s = (cudaStream_t)stream;
     int rc = grow(c, &c->st_dets, &c->st_dets_bytes, (size_t)(n_src + n_dst) * 8);
     if (rc != AXB_OK) return rc;
@@ -228,8 +244,8 @@ int axb_cost_matrix(axb_ctx* c, const uint32_t* mask_bits_dev, int H, int W,
     memset(&pd, 0, sizeof pd);
     pd.mask_idx = 0; pd.src_off = 0; pd.n_src = n_src; pd.dst_off = n_src; pd.n_dst = n_dst; pd.out_off = 0;
     AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, &pd, sizeof pd, cudaMemcpyHostToDevice, s));   // pageable source: staged before return
-    return axb_cost_matrix_batch(c, mask_bits_dev, 1, H, W, c->st_dets, c->st_pairs, 1, n_src, max_px,
-                                 path_len_dev, unreachable_dev, wcost_dev, stream);
+    return axb_cost_matrix_batch(c, mask_bits_dev, 1, H, W, c->st_dets, n_src + n_dst, c->st_pairs, 1, n_src, max_px,
+                                 path_len_dev, unreachable_dev, wcost_dev, (int64_t)n_src * n_dst, stream);
 }
 
 int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_masks, int H, int W,
@@ -251,7 +267,7 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
         total_src += pd.n_src;
     }
     if (total_src > 0x7fffffffLL) return bad_arg(c, "axb_cost_matrix_batch_host: too many sources");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     cudaStream_t s = c->own_stream;
     const size_t mask_bytes = (size_t)n_masks * H * W;
     const size_t bits_bytes = (size_t)n_masks * H * ((W + 31) / 32) * 4;
@@ -268,8 +284,8 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
     AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, pairs_host, (size_t)n_pairs * sizeof(axb_pair_desc), cudaMemcpyHostToDevice, s));
     if ((rc = axb_pack_mask(c, c->st_mask, n_masks, H, W, c->st_bits, s)) != AXB_OK) return rc;
     if (total_out > 0 && total_src > 0) {
-        rc = axb_cost_matrix_batch(c, c->st_bits, n_masks, H, W, c->st_dets, c->st_pairs, n_pairs, (int)total_src,
-                                   max_px, c->st_plen, c->st_unr, wcost_host ? c->st_wc : nullptr, s);
+        rc = axb_cost_matrix_batch(c, c->st_bits, n_masks, H, W, c->st_dets, n_dets, c->st_pairs, n_pairs, (int)total_src,
+                                   max_px, c->st_plen, c->st_unr, wcost_host ? c->st_wc : nullptr, (int64_t)total_out, s);
         if (rc != AXB_OK) return rc;
         AXB_CUDA(c, cudaMemcpyAsync(path_len_host, c->st_plen, (size_t)total_out * 4, cudaMemcpyDeviceToHost, s));
         AXB_CUDA(c, cudaMemcpyAsync(unreachable_host, c->st_unr, (size_t)total_out, cudaMemcpyDeviceToHost, s));
@@ -319,7 +335,7 @@ int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
         return bad_arg(c, "axb_decode_nms: NULL pointer");
     const long long ncell_ll = (long long)ntiles * Sx * Sy;
     if (ncell_ll > (1 << 24)) return bad_arg(c, "axb_decode_nms: more than 2^24 grid cells per frame");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     const int ncell = (int)ncell_ll;
     int npad = 1;
     while (npad < ncell) npad <<= 1;
@@ -347,7 +363,7 @@ int axb_decode_nms_host(axb_ctx* c, const float* Y_host, const int32_t* tile_yx_
     if (F == 0) return AXB_OK;
     if (!Y_host || !tile_yx_host || !n_pre_host || !conf_host || !yx_host || !keep_idx_host || !n_out_host)
         return bad_arg(c, "axb_decode_nms_host: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     cudaStream_t s = c->own_stream;
     auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
     const size_t nY = (size_t)F * ntiles * Sx * Sy * 3 * 4, nT = (size_t)ntiles * 8, nFC = (size_t)F * cap * 4, nF = (size_t)F * 4;
@@ -385,7 +401,7 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     if (max_px < 1 || max_px > AXB_MAX_PX) return bad_arg(c, "axb_trace_paths: max_px outside [1, AXB_MAX_PX]");
     if (n_req == 0) return AXB_OK;
     if (!mask_bits_dev || !req_host || !path_yx_dev || !path_len_dev) return bad_arg(c, "axb_trace_paths: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     cudaStream_t s = (cudaStream_t)stream;
     int rc = ensure_k2(c, n_req, n_req);
     if (rc != AXB_OK) return rc;
@@ -417,7 +433,8 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     int* const work_prefix = c->prefix_dev;
     int* const all_prefix = c->prefix_dev + c->prefix_cap;
     int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
-    axb::launch_k2_prep(c->st_pairs, n_req, work_prefix, all_prefix, next_same, c->counters, s);
+    axb::launch_k2_prep(c->st_pairs, n_req, work_prefix, all_prefix, next_same, c->counters, n_masks, 2 * n_req, n_req,
+                        n_req, c->status_dev + 1, s);
     c->last_n_pairs = n_req;
     // every request goes straight to the all-levels kernel: gen_list = 0 .. n-1, counters[1] = n
     AXB_CUDA(c, cudaMemcpyAsync(c->gen_list, iota.data(), (size_t)n_req * sizeof(int), cudaMemcpyHostToDevice, s));
@@ -444,7 +461,7 @@ int axb_feature_hist(axb_ctx* c, const float* image_dev, int H, int W, const int
         return bad_arg(c, "axb_feature_hist: bad size, bins outside [1, AXB_MAX_BINS] or empty range");
     if (n_boxes == 0) return AXB_OK;
     if (!image_dev || !boxes_dev || !out_dev) return bad_arg(c, "axb_feature_hist: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     axb::launch_k5(image_dev, H, W, boxes_dev, n_boxes, bins, lo, hi, out_dev, (cudaStream_t)stream);
     c->launches += 1;
     AXB_CUDA(c, cudaGetLastError());
@@ -455,12 +472,12 @@ int axb_transition_cost_batch(axb_ctx* c, const int32_t* path_len_dev, const axb
                               int max_elems_per_pair, const double* cost_tab_dev, const int64_t* arc_tab_dev,
                               int n_gaps, int max_px, double* cost_dev, int64_t* arc_dev, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
-    if (n_pairs < 0 || n_gaps <= 0 || max_px < 1 || max_px > 65535 || max_elems_per_pair < 0)
-        return bad_arg(c, "axb_transition_cost_batch: bad size");
+    if (n_pairs < 0 || n_gaps <= 0 || max_px < 1 || max_px > AXB_MAX_PX || max_elems_per_pair < 0)
+        return bad_arg(c, "axb_transition_cost_batch: bad size or max_px outside [1, AXB_MAX_PX]");
     if (n_pairs == 0 || max_elems_per_pair == 0) return AXB_OK;
     if (!path_len_dev || !pairs_dev || !cost_tab_dev || !cost_dev || (arc_tab_dev && !arc_dev))
         return bad_arg(c, "axb_transition_cost_batch: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     axb::launch_k3(path_len_dev, pairs_dev, n_pairs, cost_tab_dev, (const long long*)arc_tab_dev, n_gaps, max_px,
                    cost_dev, arc_tab_dev ? (long long*)arc_dev : nullptr, c->status_dev + 1, max_elems_per_pair,
                    (cudaStream_t)stream);
@@ -475,7 +492,7 @@ int axb_tile_nonempty(axb_ctx* c, const float* X_dev, int T, int C, int H, int W
     if (T < 0 || C < 1 || H <= 0 || W <= 0 || tilesize < 1 || T > 65535) return bad_arg(c, "axb_tile_nonempty: bad size");
     if (T == 0) return AXB_OK;
     if (!X_dev || !nonempty_dev) return bad_arg(c, "axb_tile_nonempty: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     const size_t n_flags = (size_t)((H + tilesize - 1) / tilesize) * ((W + tilesize - 1) / tilesize) * T;
     int rc = grow(c, &c->k6_flags, &c->k6_flags_bytes, n_flags * axb::kK6FlagStride * sizeof(uint32_t));
     if (rc != AXB_OK) return rc;
@@ -494,7 +511,7 @@ int axb_gather_frametiles(axb_ctx* c, const float* X_dev, int T, int C, int H, i
     if (chan_lo < 0 || chan_n < 1 || chan_lo + chan_n > C) return bad_arg(c, "axb_gather_frametiles: channel range outside [0, C)");
     if (ntiles == 0 || n_frames == 0) return AXB_OK;
     if (!X_dev || !tile_yx_dev || !frames_dev || !out_dev) return bad_arg(c, "axb_gather_frametiles: NULL pointer");
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     axb::launch_k6_gather(X_dev, T, C, H, W, tilesize, tile_yx_dev, ntiles, frames_dev, n_frames, temporal_context, chan_lo,
                           chan_n, out_dev, c->status_dev + 1, c->num_sms, (cudaStream_t)stream);
     c->launches += 1;
@@ -504,7 +521,7 @@ int axb_gather_frametiles(axb_ctx* c, const float* X_dev, int T, int C, int H, i
 
 int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     if (!c) return AXB_ERR_BAD_ARG;
-    AXB_CUDA(c, cudaSetDevice(c->device));
+    AXB_ON_DEVICE(c);
     cudaStream_t s = (cudaStream_t)stream;
     AXB_CUDA(c, cudaMemcpyAsync(c->status_host, c->status_dev, 16, cudaMemcpyDeviceToHost, s));
     AXB_CUDA(c, cudaStreamSynchronize(s));
@@ -533,6 +550,7 @@ int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     else if (flags & 4ull) rc = AXB_ERR_CAPACITY;
     else if (flags & 8ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_transition_cost_batch: path length or time gap outside its table"; }
     else if (flags & 16ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_gather_frametiles: a frame's temporal context leaves the timelapse"; }
+    else if (flags & 32ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_cost_matrix_batch: a pair descriptor points outside the detections / masks / outputs, or total_src is smaller than the pairs' sources"; }
     if (key != ~0ull || flags) {
         c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
         AXB_CUDA(c, cudaMemcpyAsync(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice, s));

@@ -111,7 +111,8 @@ inline bool first_use_on_device(unsigned long long& flags) {
 }
 
 void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
-                    int* next_same, int* counters, cudaStream_t stream);
+                    int* next_same, int* counters, int n_masks, int n_dets, long long out_capacity, int total_src,
+                    unsigned long long* err_flags, cudaStream_t stream);
 void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);

@@ -502,25 +502,44 @@ __global__ void __launch_bounds__(256) k2_all_to_general_kernel(const int* __res
 //   the targets differ.  prev/next link same-key pairs inside a +-kChainWindow index window; a
 //   pair whose depth in its list is a multiple of kMaxChain leads a chain of <= kMaxChain pairs.
 constexpr int kChainWindow = 16;
+struct PrepLimits {
+    int n_masks, n_dets;            // mask_idx in [0, n_masks), detection rows in [0, n_dets]
+    long long out_capacity;         // out_off + n_src * n_dst <= out_capacity
+    int total_src;                  // capacity of the deferred-work lists (sum of n_src the caller sized them for)
+};
+__device__ __forceinline__ bool pair_ok(const axb_pair_desc& a, const PrepLimits& lim) {
+    return a.n_src >= 0 && a.n_dst >= 0 && a.src_off >= 0 && a.dst_off >= 0 &&
+           (long long)a.src_off + a.n_src <= lim.n_dets && (long long)a.dst_off + a.n_dst <= lim.n_dets &&
+           a.mask_idx >= 0 && a.mask_idx < lim.n_masks && a.out_off >= 0 &&
+           a.out_off + (long long)a.n_src * a.n_dst <= lim.out_capacity;
+}
+// A descriptor that points outside the caller's buffers gets no work (and status flag 32): the search
+// kernels never see it.  Same when the pairs hold more sources than the work lists were sized for.
 __global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __restrict__ pairs, int n_pairs,
                                                          int* __restrict__ work_prefix, int* __restrict__ all_prefix,
-                                                         int* __restrict__ next_same, int* __restrict__ counters) {
+                                                         int* __restrict__ next_same, int* __restrict__ counters,
+                                                         const PrepLimits lim, unsigned long long* __restrict__ err_flags) {
     __shared__ int s_carry[2];
     __shared__ int s_warp[2][32];
+    __shared__ int s_bad;
     const int tid = threadIdx.x;
     int* const prev = work_prefix;            // scratch until the scan overwrites it
     if (tid < 8) counters[tid] = 0;
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
     for (int i = tid; i < n_pairs; i += blockDim.x) {
         const axb_pair_desc a = pairs[i];
         int pv = -1, nx = -1;
-        if (a.n_src > 0) {
+        const bool ok = pair_ok(a, lim);
+        if (!ok) s_bad = 1;
+        if (ok && a.n_src > 0) {
             for (int q = i - 1; q >= max(0, i - kChainWindow); --q) {
                 const axb_pair_desc b = pairs[q];
-                if (b.mask_idx == a.mask_idx && b.src_off == a.src_off && b.n_src == a.n_src) { pv = q; break; }
+                if (b.mask_idx == a.mask_idx && b.src_off == a.src_off && b.n_src == a.n_src && pair_ok(b, lim)) { pv = q; break; }
             }
             for (int q = i + 1; q <= min(n_pairs - 1, i + kChainWindow); ++q) {
                 const axb_pair_desc b = pairs[q];
-                if (b.mask_idx == a.mask_idx && b.src_off == a.src_off && b.n_src == a.n_src) { nx = q; break; }
+                if (b.mask_idx == a.mask_idx && b.src_off == a.src_off && b.n_src == a.n_src && pair_ok(b, lim)) { nx = q; break; }
             }
         }
         prev[i] = pv;
@@ -538,7 +557,8 @@ __global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __re
     __syncthreads();
     for (int base = 0; base < n_pairs; base += blockDim.x) {
         const int i = base + tid;
-        const int na = i < n_pairs ? max(pairs[i].n_src, 0) : 0;
+        int na = 0;
+        if (i < n_pairs) { const axb_pair_desc a = pairs[i]; na = pair_ok(a, lim) ? a.n_src : 0; }
         const int nw = (i < n_pairs && all_prefix[i]) ? na : 0;
         int xa = na, xw = nw;
         for (int o = 1; o < 32; o <<= 1) {
@@ -565,12 +585,20 @@ __global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __re
         if (tid == (int)blockDim.x - 1) { s_carry[0] = incla; s_carry[1] = inclw; }
         __syncthreads();
     }
-    if (tid == 0) { all_prefix[n_pairs] = s_carry[0]; work_prefix[n_pairs] = s_carry[1]; }
+    if (tid == 0) {
+        const bool over = s_carry[1] > lim.total_src;        // the deferred-work lists would overflow: no work at all
+        all_prefix[n_pairs] = s_carry[0];
+        work_prefix[n_pairs] = over ? 0 : s_carry[1];
+        if (s_bad || over) atomicOr(err_flags, 32ull);
+    }
 }
 
 void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
-                    int* next_same, int* counters, cudaStream_t stream) {
-    k2_prep_kernel<<<1, 1024, 0, stream>>>(pairs, n_pairs, work_prefix, all_prefix, next_same, counters);
+                    int* next_same, int* counters, int n_masks, int n_dets, long long out_capacity, int total_src,
+                    unsigned long long* err_flags, cudaStream_t stream) {
+    PrepLimits lim;
+    lim.n_masks = n_masks; lim.n_dets = n_dets; lim.out_capacity = out_capacity; lim.total_src = total_src;
+    k2_prep_kernel<<<1, 1024, 0, stream>>>(pairs, n_pairs, work_prefix, all_prefix, next_same, counters, lim, err_flags);
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {

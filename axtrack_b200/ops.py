@@ -26,8 +26,10 @@ def get_context(device=None):
     return _contexts[idx]
 
 
-def _stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+def _stream(device=None):
+    """torch's current stream ON THE TENSORS' DEVICE (not on torch's current device: the C ABI runs on
+    the ctx's device and a stream of another device is an invalid handle there)."""
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
 def _need_cuda(t, name, dtype=None):
@@ -54,7 +56,7 @@ def pack_mask(mask):
     n, H, W = mask.shape
     ctx = get_context(mask.device)
     bits = torch.empty((n, H, mask_words(W)), dtype=torch.int32, device=mask.device)
-    ctx.check(ctx.lib.axb_pack_mask(ctx.handle, mask.data_ptr(), n, H, W, bits.data_ptr(), _stream()))
+    ctx.check(ctx.lib.axb_pack_mask(ctx.handle, mask.data_ptr(), n, H, W, bits.data_ptr(), _stream(mask.device)))
     return bits
 
 
@@ -67,7 +69,7 @@ def pack_weights(weights):
     n, H, W = weights.shape
     ctx = get_context(weights.device)
     bits = torch.empty((n, H, mask_words(W)), dtype=torch.int32, device=weights.device)
-    ctx.check(ctx.lib.axb_pack_weights(ctx.handle, weights.data_ptr(), n, H, W, bits.data_ptr(), _stream()))
+    ctx.check(ctx.lib.axb_pack_weights(ctx.handle, weights.data_ptr(), n, H, W, bits.data_ptr(), _stream(weights.device)))
     return bits
 
 
@@ -99,11 +101,12 @@ def cost_matrix_batch(mask_bits, W, dets_yx, pairs, max_px=500, want_cost=True, 
         if pairs_dev is None:
             pairs_dev = torch.from_numpy(pairs.view(np.uint8).reshape(-1).copy()).to(dev, non_blocking=False)
         n_masks, H, _ = mask_bits.shape
+        cap_out = min(int(path_len.numel()), int(unreach.numel()), int(wcost.numel()) if wcost is not None else 1 << 62)
         ctx.check(ctx.lib.axb_cost_matrix_batch(
-            ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), dets_yx.data_ptr(),
+            ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), dets_yx.data_ptr(), int(dets_yx.shape[0]),
             pairs_dev.data_ptr(), n_pairs, total_src, int(max_px),
             path_len.data_ptr(), unreach.data_ptr(), wcost.data_ptr() if wcost is not None else None,
-            _stream()))
+            cap_out, _stream(dev)))
     return path_len[:total], unreach[:total], (wcost[:total] if wcost is not None else None), pairs
 
 
@@ -125,7 +128,7 @@ def cost_matrix(mask_bits, W, src_yx, dst_yx, max_px=500, want_cost=True):
         ctx.check(ctx.lib.axb_cost_matrix(
             ctx.handle, mask_bits.data_ptr(), mask_bits.shape[0], int(W), src_yx.data_ptr(), ns,
             dst_yx.data_ptr(), nd, int(max_px), path_len.data_ptr(), unreach.data_ptr(),
-            wcost.data_ptr() if wcost is not None else None, _stream()))
+            wcost.data_ptr() if wcost is not None else None, _stream(dev)))
     return path_len, unreach, wcost
 
 
@@ -162,7 +165,7 @@ def decode_nms(Y, tile_yx, tilesize=512, conf_thr=0.55, nms_dist=23, cap=None, w
         ctypes.c_float(float(np.float32(conf_thr))), int(nms_dist), int(cap),
         ptr('pre_conf'), ptr('pre_yx'), ptr('pre_cell'), o['n_pre'].data_ptr(),
         o['conf'].data_ptr(), o['yx'].data_ptr(), o['keep_idx'].data_ptr(), o['n_out'].data_ptr(),
-        _stream()))
+        _stream(dev)))
     return o
 
 
@@ -170,7 +173,7 @@ def raise_status(pairs=None, dets_yx_host=None, device=None):
     """Synchronise and raise the reference's exception for the first input error, if any
     (astar_wrapper.py:35-45: ValueError for weights < 1, out-of-grid start / goal)."""
     ctx = get_context(device)
-    rc, (p, i, j) = ctx.status(_stream())
+    rc, (p, i, j) = ctx.status(_stream(torch.device('cuda', ctx.device)))
     if rc == _lib.OK:
         return
     if rc == _lib.ERR_BAD_WEIGHT:
@@ -219,7 +222,7 @@ def transition_cost_batch(path_len, pairs, cost_tab, arc_tab=None, pairs_dev=Non
         ctx.check(ctx.lib.axb_transition_cost_batch(
             ctx.handle, path_len.data_ptr(), pairs_dev.data_ptr(), n_pairs, max_elems,
             cost_tab.data_ptr(), arc_tab.data_ptr() if arc_tab is not None else None, int(n_gaps), int(n_d - 1),
-            cost.data_ptr(), arc.data_ptr() if arc is not None else None, _stream()))
+            cost.data_ptr(), arc.data_ptr() if arc is not None else None, _stream(dev)))
     return cost, arc
 
 
@@ -242,7 +245,7 @@ def trace_paths(mask_bits, W, requests, max_px=500):
     if n:
         n_masks, H, _ = mask_bits.shape
         ctx.check(ctx.lib.axb_trace_paths(ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), req.ctypes.data, n,
-                                          int(max_px), yx.data_ptr(), ln.data_ptr(), _stream()))
+                                          int(max_px), yx.data_ptr(), ln.data_ptr(), _stream(dev)))
     return yx, ln
 
 
@@ -262,7 +265,7 @@ def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
     if n:
         H, W = image.shape
         ctx.check(ctx.lib.axb_feature_hist(ctx.handle, image.data_ptr(), int(H), int(W), boxes.data_ptr(), n,
-                                           int(bins), float(lo), float(hi), out.data_ptr(), _stream()))
+                                           int(bins), float(lo), float(hi), out.data_ptr(), _stream(dev)))
     return out
 
 
@@ -282,7 +285,7 @@ def tile_nonempty(X, tilesize=512):
     ctx = get_context(X.device)
     out = torch.empty((yt * xt, T), dtype=torch.uint8, device=X.device)
     ctx.check(ctx.lib.axb_tile_nonempty(ctx.handle, X.data_ptr(), int(T), int(C), int(H), int(W), int(tilesize),
-                                        out.data_ptr(), _stream()))
+                                        out.data_ptr(), _stream(X.device)))
     return out.view(yt, xt, T).bool()
 
 
@@ -313,5 +316,5 @@ def gather_frametiles(X, tile_yx, frames, tilesize=512, temporal_context=2, use_
                       dtype=torch.float32, device=X.device)
     ctx.check(ctx.lib.axb_gather_frametiles(ctx.handle, X.data_ptr(), int(T), int(C), int(H), int(W), int(tilesize),
                                             tile_yx.data_ptr(), int(nt), frames.data_ptr(), int(B),
-                                            int(temporal_context), int(lo), int(nch), out.data_ptr(), _stream()))
+                                            int(temporal_context), int(lo), int(nch), out.data_ptr(), _stream(X.device)))
     return out

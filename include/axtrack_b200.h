@@ -8,9 +8,15 @@
  *   - all `*_dev` pointers are CUDA device pointers owned by the caller (e.g. torch tensors);
  *     `*_host` pointers are host memory (pinned for best speed); nothing is allocated for the
  *     caller and nothing is kept after the call returns except ctx-owned scratch;
- *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream); device
- *     entry points are asynchronous on that stream; one ctx may be used from one thread at a
- *     time (create one ctx per thread / per stream for concurrency);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream) and must belong
+ *     to the ctx's device; device entry points are asynchronous on that stream.  The ctx owns the
+ *     scratch of the calls in flight, so ONE ctx serves ONE stream at a time: issue the calls of a
+ *     ctx on one stream (or order them yourself), and create one ctx per thread / per concurrent
+ *     stream.  Every entry point selects the ctx's device and restores the calling thread's
+ *     current device before it returns;
+ *   - the device-side status is sticky PER CTX until axb_status() reads it: a flag raised by one
+ *     call (e.g. AXB_ERR_CAPACITY of axb_decode_nms) is reported by the next axb_status() or
+ *     *_host entry point on that ctx, whichever comes first;
  *   - return value: AXB_OK or a negative AXB_ERR_* code.  Input errors that the reference
  *     raises from inside pyastar2d (out-of-grid start / goal, astar_wrapper.py:39-45) are
  *     detected on the device and reported by axb_status() after the stream has drained;
@@ -92,15 +98,20 @@ int axb_pack_weights(axb_ctx* ctx, const float* weights_dev, int n_masks, int H,
  *               search hit the max_path_length cut-off, astar.cpp:88-92), else 0
  *   wcost       float32 (optional, may be NULL) cost of the returned path = sum of weights over
  *               path[1:] (astar.cpp:122), +inf where unreachable
- * dets_yx_dev: int32 [n, 2] rows (y, x).  pairs_dev: n_pairs descriptors in DEVICE memory.
- * total_src = sum of n_src over the pairs (host value, sizes the work list). */
+ * dets_yx_dev: int32 [n_dets, 2] rows (y, x).  pairs_dev: n_pairs descriptors in DEVICE memory.
+ * total_src = sum of n_src over the pairs (host value, sizes the work list); out_capacity = elements
+ * each output buffer holds.  The descriptors are validated on the device before any search runs
+ * (the pair loop of AxonDetections.py:553-566 cannot index outside its own lists; a C caller can):
+ * a pair with a negative count, detections outside [0, n_dets], mask_idx outside [0, n_masks) or
+ * an output block outside [0, out_capacity) gets no work and sets AXB_ERR_BAD_ARG in axb_status,
+ * as does a total_src smaller than the pairs' sources (then nothing runs). */
 int axb_cost_matrix_batch(axb_ctx* ctx,
                           const uint32_t* mask_bits_dev, int n_masks, int H, int W,
-                          const int32_t* dets_yx_dev,
+                          const int32_t* dets_yx_dev, int n_dets,
                           const axb_pair_desc* pairs_dev, int n_pairs, int total_src,
                           int max_px,
                           int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev,
-                          void* stream);
+                          int64_t out_capacity, void* stream);
 
 /* Single frame pair, device buffers (a 1-element batch). */
 int axb_cost_matrix(axb_ctx* ctx, const uint32_t* mask_bits_dev, int H, int W,

@@ -174,6 +174,65 @@ def test_out_of_grid_errors(cuda):
         ops.raise_status()
 
 
+def test_bad_pair_descriptors_get_no_work(cuda):
+    """the DEVICE entry point validates its descriptors -- a pair that points outside the
+    detections / masks / outputs gets no work and sets AXB_ERR_BAD_ARG; the valid pairs of the same batch
+    are still answered; a total_src smaller than the pairs' sources runs nothing."""
+    from axtrack_b200 import ops, _lib
+    mask = synth.make_mask(300, 320, 2, pitch=(50, 90), width=(5, 10))
+    a, b = synth.make_tracks(mask, 20, 2, 2)
+    dets = np.concatenate([a, b]).astype(np.int32)
+    bits = ops.pack_mask(cuda.from_numpy(mask.astype(np.uint8)).cuda())
+    dd = cuda.from_numpy(dets).cuda()
+    good = (0, 0, len(a), len(a), len(b))
+    ref = oracle.cost_matrix_rule(mask, a, b, 200)
+    n = len(a) * len(b)
+    for bad in [(0, 0, len(a), len(a), len(b) + 1),        # targets run past the detections
+                (0, -1, 3, 0, 3), (1, 0, 3, 0, 3)]:         # negative offset, mask index out of range
+        pairs, total, _ = ops.make_pairs([good, bad])
+        out = (cuda.full((total,), -7, dtype=cuda.int32).cuda(), cuda.full((total,), 9, dtype=cuda.uint8).cuda(), None)
+        pl, un, _, _ = ops.cost_matrix_batch(bits, 320, dd, pairs, 200, want_cost=False, out=out)
+        with pytest.raises(_lib.AxbError, match='pair descriptor'):
+            ops.raise_status()
+        ops.raise_status()
+        assert np.array_equal(pl[:n].cpu().numpy().reshape(ref[0].shape), ref[0]), bad
+        assert (out[0][n:] == -7).all() and (out[1][n:] == 9).all(), bad
+    # output block outside the buffers: out_capacity is what the caller's tensors hold
+    pairs, total, _ = ops.make_pairs([good])
+    small = (cuda.full((n - 1,), -7, dtype=cuda.int32).cuda(), cuda.full((n - 1,), 9, dtype=cuda.uint8).cuda(), None)
+    ops.cost_matrix_batch(bits, 320, dd, pairs, 200, want_cost=False, out=small)
+    with pytest.raises(_lib.AxbError, match='pair descriptor'):
+        ops.raise_status()
+    assert (small[0] == -7).all()
+    # total_src too small for the pairs' sources: nothing runs
+    ctx = ops.get_context()
+    pd = cuda.from_numpy(pairs.view(np.uint8).reshape(-1).copy()).cuda()
+    out = (cuda.full((n,), -7, dtype=cuda.int32).cuda(), cuda.full((n,), 9, dtype=cuda.uint8).cuda())
+    ctx.check(ctx.lib.axb_cost_matrix_batch(ctx.handle, bits.data_ptr(), 1, 300, 320, dd.data_ptr(), len(dets), pd.data_ptr(), 1,
+                                            len(a) - 1, 200, out[0].data_ptr(), out[1].data_ptr(), None, n, None))
+    cuda.cuda.synchronize()
+    with pytest.raises(_lib.AxbError, match='total_src'):
+        ops.raise_status()
+    assert (out[0] == -7).all()
+
+
+def test_entry_points_keep_the_callers_device(cuda):
+    """tensors on another device than torch's current one -- the call runs on the tensors'
+    device with that device's stream and leaves the thread's current device alone."""
+    if cuda.cuda.device_count() < 2:
+        pytest.skip('needs two visible GPUs')
+    from axtrack_b200 import ops
+    mask = synth.make_mask(300, 320, 2, pitch=(50, 90), width=(5, 10))
+    a, b = synth.make_tracks(mask, 20, 2, 2)
+    cuda.cuda.set_device(0)
+    d1 = cuda.device('cuda', 1)
+    bits = ops.pack_mask(cuda.from_numpy(mask.astype(np.uint8)).to(d1))
+    pl, un, wc = ops.cost_matrix(bits, 320, cuda.from_numpy(a).to(d1), cuda.from_numpy(b).to(d1), 200)
+    ops.raise_status(device=d1)
+    assert cuda.cuda.current_device() == 0
+    _check((pl.cpu().numpy(), un.cpu().numpy(), wc.cpu().numpy()), oracle.cost_matrix_rule(mask, a, b, 200))
+
+
 @pytest.mark.parametrize('seed', [0, 1])
 def test_timelapse_pipeline_vs_oracle(cuda, seed):
     """decode+NMS of all frames then all (t, t_bef) cost matrices, vs the oracle; corridor mask."""
