@@ -46,16 +46,18 @@ MAX_MISSES = 1        # deployed MCF_MAX_NUM_MISSES
 # --------------------------------------------------------------------------------------------
 # synthetic workload
 # --------------------------------------------------------------------------------------------
-def make_block(wl, rank, seed=0):
-    """(mask bool[H,W], Y f32 [Tb,ntiles,12,12,3], tile_yx, t0): rank's block of the timelapse;
-    ranks > 0 carry a 2-frame halo in front (t0 = 2)."""
-    from axtrack_b200 import synth
-    H, W, T = wl['H'], wl['W'], wl['T']
+def make_block(wl, rank=0, world=1, seed=0):
+    """(mask bool[H,W], Y f32 [Tb,ntiles,12,12,3], tile_yx, t0, block): rank's block of ONE synthetic
+    timelapse of T * world frames (every rank derives the same timelapse from the seed and cuts its
+    block out of it with sharding.partition, so a halo frame IS the neighbour rank's frame);
+    ranks > 0 carry the 2-frame halo in front (t0 = 2).  block = (first, own, stop) in global frames."""
+    from axtrack_b200 import synth, sharding
+    H, W, T = wl['H'], wl['W'], wl['T'] * world
     mask = synth.make_mask(H, W, seed)
-    t0 = 0 if rank == 0 else MAX_MISSES + 1
-    tracks = synth.make_tracks(mask, wl['n_dets'], T + t0, seed + 17 * rank)
-    Y = np.stack([synth.make_head_tensor(tracks[t], H, W, seed + 1000 * rank + t)[0] for t in range(T + t0)])
-    return mask, Y, synth.tile_table(H, W), t0
+    tracks = synth.make_tracks(mask, wl['n_dets'], T, seed)
+    first, own, stop = sharding.partition(T, world, MAX_MISSES)[rank]
+    Y = np.stack([synth.make_head_tensor(tracks[t], H, W, seed + t)[0] for t in range(first, stop)])
+    return mask, Y, synth.tile_table(H, W), own - first, (first, own, stop)
 
 
 def ball_cells(dets_yx, H, W, r):
@@ -179,7 +181,7 @@ def run_reference(args, wl):
     if rank != 0:
         return
     sub = dict(wl, T=3)
-    mask, Y, tile_yx, _ = make_block(sub, 0)
+    mask, Y, tile_yx, _, _ = make_block(sub)
     frame_dets = oracle_frame_dets(Y, tile_yx)
     keys = frame_pair_keys(3, MAX_MISSES)
     cpp = inrange_calls_per_pair(frame_dets, keys)
@@ -210,6 +212,109 @@ def run_reference(args, wl):
 # --------------------------------------------------------------------------------------------
 # B200 arm
 # --------------------------------------------------------------------------------------------
+class Job:
+    """One workload on this rank: its block of the synthetic timelapse resident in HBM, and the step
+    that is timed.  N = 1: pipeline.associate_frames.  N > 1: sharding.associate_sharded -- the product
+    entry -- on ONE timelapse of T * N frames cut by sharding.partition, every rank's K2 kernels
+    storing straight into rank 0's HBM (PeerSlabs) or NCCL sends after the kernels (--gather nccl)."""
+
+    def __init__(self, wl, dev, rank, world, gather):
+        import torch
+        import torch.distributed as dist
+        from axtrack_b200 import sharding
+        self.torch, self.dist, self.wl, self.dev, self.rank, self.world = torch, dist, wl, dev, rank, world
+        self.mask, self.Y, self.tile_yx, self.t0, self.block = make_block(wl, rank, world)
+        self.T_total = wl['T'] * world
+        first, own, stop = self.block
+        H, W = self.mask.shape
+        ntiles = len(self.tile_yx)
+        self.td = torch.from_numpy(self.tile_yx).to(dev)
+        self.md = torch.from_numpy(self.mask.astype(np.uint8)).to(dev)
+        if world == 1:
+            self.Yd = torch.from_numpy(self.Y).to(dev)
+        else:       # the whole timelapse's head tensor as associate_sharded takes it; only this rank's rows are filled
+            self.Yd = torch.zeros((self.T_total, ntiles) + self.Y.shape[2:], dtype=torch.float32, device=dev)
+            self.Yd[first:stop].copy_(torch.from_numpy(self.Y))
+        self.slabs = None
+        if world > 1 and gather == 'peer':
+            try:
+                self.slabs = sharding.PeerSlabs(dev)
+            except Exception as e:                   # no peer mapping on this box: every rank falls back together
+                print(f'[bench] rank {rank}: peer slabs unavailable ({e!r}); using the NCCL gather', file=sys.stderr)
+            ok = torch.tensor([1 if self.slabs is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                self.slabs = None
+
+    def step(self, to_host=False):
+        from axtrack_b200 import pipeline, sharding
+        if self.world == 1:
+            return None, pipeline.associate_frames(self.Yd, self.td, self.md, max_px=MAX_PX, max_num_misses=MAX_MISSES,
+                                                   want_cost=False)
+        return sharding.associate_sharded(self.Yd, self.td, self.md, max_px=MAX_PX, max_num_misses=MAX_MISSES,
+                                          slabs=self.slabs, to_host=to_host)
+
+    def sync_all(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def timed(self, steps, warmup, flush, ctx=None, sampler=None):
+        """-> (ms summed over the steps [max over ranks], frame pairs of all ranks per step, launches, last res)"""
+        torch, dist = self.torch, self.dist
+        for _ in range(max(warmup, 3)):
+            _, res = self.step()
+        if self.slabs is not None:           # sized by the warm-up: the timed steps need no sizing collective / host sync
+            self.slabs.collective_sizing = False
+        self.sync_all()
+        if sampler is not None:
+            sampler.start()
+        l0 = ctx.launches if ctx is not None else 0
+        evs = []
+        self.sync_all()
+        for _ in range(steps):
+            flush.fill_(1)                               # L2 flush between timed iterations (untimed)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _, res = self.step()
+            e1.record()
+            evs.append((e0, e1))
+        self.sync_all()
+        launches = (ctx.launches - l0) if ctx is not None else 0
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([ms, float(len(res.keys))], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+            return float(tm[0]), float(ts[1]), launches, res
+        return ms, float(len(res.keys)), launches, res
+
+    def verify_gather(self):
+        """Outside the timed region: what rank 0 assembled from the gather equals what every rank computes
+        for its own block into LOCAL buffers (per-pair sums of path_len and of the flags)."""
+        from axtrack_b200 import sharding
+        if self.world == 1:
+            return None
+        if self.slabs is not None:
+            self.slabs.collective_sizing = True
+        got, _ = self.step(to_host=True)
+        local = sharding.associate_block(self.block, self.Yd, self.td, self.md, MAX_PX, MAX_MISSES).pair_matrices()
+        mine = {(k[0] + self.block[0], k[1] + self.block[0]): (int(v[0].sum()), int(v[1].sum()), v[0].shape) for k, v in local.items()}
+        allsums = [None] * self.world
+        self.dist.all_gather_object(allsums, mine)
+        if self.rank != 0:
+            return None
+        want = {}
+        for d in allsums:
+            want.update(d)
+        from axtrack_b200.host import frame_pair_keys
+        assert list(got) == frame_pair_keys(self.T_total, MAX_MISSES), 'assembled keys are not the reference loop order'
+        for k, (spl, sun, shp) in want.items():
+            assert got[k][0].shape == shp and int(got[k][0].sum()) == spl and int(got[k][1].sum()) == sun, k
+        return len(got)
+
+
 def run_b200(args, wl):
     import torch
     import torch.distributed as dist
@@ -225,83 +330,23 @@ def run_b200(args, wl):
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
 
-    mask, Y, tile_yx, t0 = make_block(wl, rank)
+    job = Job(wl, dev, rank, world, args.gather)
+    mask, Y, tile_yx = job.mask, job.Y, job.tile_yx
     H, W = mask.shape
-    Yd = torch.from_numpy(Y).to(dev)
-    td = torch.from_numpy(tile_yx).to(dev)
-    md = torch.from_numpy(mask.astype(np.uint8)).to(dev)
+    first, own, stop = job.block
+    Yd_block = job.Yd if world == 1 else job.Yd[first:stop]
+    td, md, slabs = job.td, job.md, job.slabs
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     ctx = ops.get_context(dev)
-
-    # N > 1: the K2 kernels of every rank store their matrices straight into rank 0's HBM over NVLink
-    # (sharding.PeerSlabs); --gather nccl = send them after the kernels instead (the round-1 baseline)
-    slabs = None
-    if world > 1 and args.gather == 'peer':
-        try:
-            slabs = sharding.PeerSlabs(dev)
-        except Exception as e:                       # no peer mapping on this box: every rank falls back together
-            print(f'[bench] rank {rank}: peer slabs unavailable ({e!r}); using the NCCL gather', file=sys.stderr)
-        ok = torch.tensor([1 if slabs is not None else 0], device=dev)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        if int(ok.item()) == 0:
-            slabs = None
-
-    def gather_to_rank0(res):
-        if world == 1:
-            return
-        shapes = torch.from_numpy(np.stack([res.pairs['n_src'], res.pairs['n_dst']], 1).astype(np.int64).reshape(-1, 2))
-        if slabs is not None:
-            slabs.publish(res.path_len.numel(), shapes)
-            if rank == 0:
-                slabs.collect()
-        else:
-            sharding.gather_to_rank0(res.path_len, res.unreachable, shapes)
-
-    def step():
-        res = pipeline.associate_frames(Yd, td, md, max_px=MAX_PX, max_num_misses=MAX_MISSES, want_cost=False, t0=t0,
-                                        out_alloc=slabs.out_alloc if slabs is not None else None)
-        gather_to_rank0(res)
-        return res
-
-    def sync_all():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    for _ in range(max(args.warmup, 3)):
-        res = step()
-    n_pairs = len(res.keys)
-    sync_all()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    l0 = ctx.launches
-    evs = []
-    sync_all()
-    for _ in range(args.steps):
-        flush.fill_(1)                                   # L2 flush between timed iterations (untimed)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        res = step()
-        e1.record()
-        evs.append((e0, e1))
-    sync_all()
-    launches = ctx.launches - l0
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, total_pairs, launches, res = job.timed(args.steps, args.warmup, flush, ctx, sampler)
     clocks = sampler.stop() if rank == 0 else None
-    ms = sum(a.elapsed_time(b) for a, b in evs)
-    t = torch.tensor([ms, float(n_pairs)], dtype=torch.float64, device=dev)
-    if world > 1:
-        tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-        ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
-        ms, total_pairs = float(tm[0]), float(ts[1])
-    else:
-        total_pairs = float(n_pairs)
     value = total_pairs * args.steps / (ms * 1e-3)
+    gathered_pairs = job.verify_gather()
 
     # ---- dominant kernel alone (K2) for the roofline: CUDA events around the launch ------------
     bits = ops.pack_mask(md)
-    det = ops.decode_nms(Yd, td)
+    det = ops.decode_nms(Yd_block, td)
     n_out = det['n_out'].cpu().numpy()
     cap = det['conf'].shape[1]
     pairs, total, _ = pipeline.build_pairs(n_out, cap, res.keys)
@@ -322,7 +367,7 @@ def run_b200(args, wl):
     for i in range(3 + args.steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        ops.decode_nms(Yd, td, want_pre=False)
+        ops.decode_nms(Yd_block, td, want_pre=False)
         e1.record()
         torch.cuda.synchronize()
         if i >= 3:
@@ -382,29 +427,28 @@ def run_b200(args, wl):
     k2 = float(np.mean(k2ms)) * 1e-3
     peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))) if os.path.exists(os.path.join(ROOT, 'MEASURED_PEAKS.json')) else {}
     peak = float(peaks.get('hbm_gbs', 6650.0))
-    traffic = None
+    traffic, traffic_src = None, None
     tf = os.path.join(ROOT, 'profiles', 'k2_dram_traffic.json')
-    if os.path.exists(tf):
+    if os.path.exists(tf) and MAX_PX == 500:      # the committed ncu captures are of max_px = 500 runs
         try:
-            traffic = json.load(open(tf)).get(args.workload)
+            tj = json.load(open(tf))
+            traffic, traffic_src = tj.get(args.workload), tj.get('source')
         except Exception:
             traffic = None
-    if MAX_PX != 500:
-        traffic = None            # the committed ncu capture is of the max_px = 500 run
-    klabel = ('K2 launch group = k2_sparse_kernel (dominant, ~90 % by the ncu launch list) + tile/prep/dense/general; one launch = all frame pairs of the block'
-              if MAX_PX <= 511 else 'K2 launch group = prep + k2_general_wide_kernel (max_px > 511: every source on the all-levels kernel, window bitmaps in global scratch)')
+    klabel = ('K2 launch group = the level-0 search kernel (dominant, > 90 % by the ncu launch list) + tile/prep/dense/general; one launch = all frame pairs of the block'
+              if MAX_PX <= 511 else 'K2 launch group at max_px > 511 (wide windows); one launch = all frame pairs of the block')
     roofline = dict(bound='hbm', kernel=klabel,
                     achieved=alg / k2 / 1e9, peak=peak, unit='GB/s', frac=alg / k2 / 1e9 / peak,
                     peak_source='MEASURED_PEAKS.json hbm_gbs (measured copy)' if peaks else 'fallback 6650 GB/s',
                     algorithmic_bytes_per_launch=alg, kernel_ms=k2 * 1e3, k1_decode_nms_ms=float(np.mean(k1ms)), k3_transition_ms=float(np.mean(k3ms)), k5_feature_hist_ms=float(np.mean(k5ms)), k6_tiling=k6,
-                    traffic=traffic)
+                    traffic=traffic, traffic_source=traffic_src)
 
-    # ---- e2e: host buffers through the C ABI ------------------------------------------------------
-    e2e = None
-    cpu = None
-    if True:
+    # ---- e2e: host buffers in, host results out ------------------------------------------------------
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    if world == 1:
+        # the reference-facing C-ABI calls with HOST buffers (numpy in / numpy out): axb_decode_nms_host +
+        # axb_cost_matrix_batch_host; H2D and D2H happen inside the library
         ha = host.HostAssociator(local)
-        pin = lambda a: torch.from_numpy(a).pin_memory().numpy()
         Yh, th, mh = pin(Y), pin(tile_yx), pin(mask.astype(np.uint8))
         F = Y.shape[0]
         dout = dict(n_pre=pin(np.zeros(F, np.int32)), n_out=pin(np.zeros(F, np.int32)), conf=pin(np.empty((F, cap), np.float32)),
@@ -418,23 +462,55 @@ def run_b200(args, wl):
             return tot
         for _ in range(3):
             tot = e2e_step()
-        sync_all()
+        torch.cuda.synchronize()
         t_0 = time.perf_counter()
         for _ in range(args.steps):
             e2e_step()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t_0
-        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         h2d = Yh.nbytes + th.nbytes + mh.nbytes + F * cap * 8 + len(res.keys) * 32
         d2h = sum(v.nbytes for v in dout.values()) + tot * 5
-        e2e = dict(value=total_pairs * args.steps / float(tt[0]), unit='frame-pairs/s', h2d_bytes_per_step=int(h2d),
-                   d2h_bytes_per_step=int(d2h), ms_per_step=1e3 * float(tt[0]) / args.steps,
+        e2e = dict(value=total_pairs * args.steps / dt, unit='frame-pairs/s', h2d_bytes_per_step=int(h2d),
+                   d2h_bytes_per_step=int(d2h), ms_per_step=1e3 * dt / args.steps,
                    api='axb_decode_nms_host + axb_cost_matrix_batch_host (numpy in/out, pinned)')
-        # parity spot check of what was timed (oracle as checker only)
+        # what was timed equals the device path's result
         assert np.array_equal(mout[0][:tot], res.path_len.cpu().numpy()) and np.array_equal(mout[1][:tot], res.unreachable.cpu().numpy())
+    else:
+        # N > 1: every rank uploads its block's inputs from pinned host memory, runs the sharded product
+        # entry, and the step ENDS ON RANK 0'S HOST: rank 0 copies every rank's gathered matrices out of its
+        # slabs into pinned memory (sharding.HostGather) inside the timed region; wall clock, max over ranks
+        Yh, th, mh = pin(Y), pin(tile_yx), pin(mask.astype(np.uint8))
+        hg = sharding.HostGather()
+        if slabs is not None:
+            slabs.collective_sizing = False
 
+        def e2e_step():
+            job.Yd[first:stop].copy_(torch.from_numpy(Yh), non_blocking=True)
+            td.copy_(torch.from_numpy(th), non_blocking=True)
+            md.copy_(torch.from_numpy(mh), non_blocking=True)
+            got, _ = sharding.associate_sharded(job.Yd, td, md, max_px=MAX_PX, max_num_misses=MAX_MISSES, slabs=slabs, to_host=hg)
+            dist.barrier()                 # the step is over when rank 0 holds the dict on its host
+            return got
+        for _ in range(3):
+            got = e2e_step()
+        job.sync_all()
+        t_0 = time.perf_counter()
+        for _ in range(args.steps):
+            got = e2e_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t_0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e = None
+        if rank == 0:
+            assert len(got) == int(total_pairs)
+            e2e = dict(value=total_pairs * args.steps / float(tt[0]), unit='frame-pairs/s',
+                       h2d_bytes_per_step=int(Yh.nbytes + th.nbytes + mh.nbytes), d2h_bytes_per_step=int(hg.bytes),
+                       ms_per_step=1e3 * float(tt[0]) / args.steps,
+                       api='sharding.associate_sharded(to_host=HostGather): per-rank H2D of its block from pinned memory, gather into rank 0 HBM, '
+                           'rank 0 D2H of ALL ranks matrices into pinned memory; h2d is per rank, d2h is rank 0')
+
+    cpu = None
     if rank == 0 and world == 1:
         t_astar, calls, t_dec, kind, ns = cpu_sample(mask, frame_dets, Y, tile_yx, args.cpu_calls)
         cpp = inrange_calls_per_pair(frame_dets, res.keys)
@@ -444,14 +520,31 @@ def run_b200(args, wl):
                            f'for the first {ns} sources of frame pair (1,0) = {calls} in-range A* calls, + numpy decode/NMS of 1 frame '
                            f'({t_dec * 1e3:.1f} ms); extrapolated to {cpp:.0f} in-range calls per frame pair'))
 
+    # ---- configs[3] as BASELINE states it: ONE 2000-frame timelapse sharded by timepoint (strong scaling) ----
+    strong = None
+    if args.strong_c4 and args.workload == 'c2' and args.scaling == 'weak' and MAX_PX == 500:
+        del job, res
+        torch.cuda.empty_cache()
+        c4 = WORKLOADS['c4']
+        wl4 = dict(c4, T=-(-c4['T'] // world))
+        j4 = Job(wl4, dev, rank, world, args.gather)
+        n4 = max(2, min(args.steps, 5))
+        ms4, pairs4, _, _ = j4.timed(n4, 3, flush)
+        g4 = j4.verify_gather()
+        strong = dict(workload=c4['desc'], frames_total=wl4['T'] * world, frames_per_gpu=wl4['T'], frame_pairs_total=int(pairs4),
+                      value=pairs4 * n4 / (ms4 * 1e-3), unit='frame-pairs/s', ms_per_step=ms4 / n4, steps=n4, scaling='strong',
+                      gathered_pairs_verified=g4)
+
     if rank == 0:
+        par = ('single GPU' if world == 1 else 'K2 stores into rank 0 HBM over NVLink (peer slabs)' if slabs is not None else 'NCCL gather to rank 0')
         line = dict(metric='frame-pairs/sec (A* cost matrix + decode/NMS)', value=value, unit='frame-pairs/s', n_gpus=world,
                     steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms / args.steps, higher_is_better=True,
                     scaling=args.scaling, vs_baseline=None, dtype='int32', data='synthetic',
-                    config=dict(workload=wl['desc'], frames_per_gpu=wl['T'], frame_pairs_total=int(total_pairs),
+                    config=dict(workload=wl['desc'], frames_per_gpu=wl['T'], frames_total=wl['T'] * world, frame_pairs_total=int(total_pairs),
                                 dets_per_frame=float(np.mean(n_out)), max_px=MAX_PX, max_num_misses=MAX_MISSES,
-                                parallelism=f'timepoint shards x{world}, ' + ('single GPU' if world == 1 else 'K2 stores into rank 0 HBM over NVLink (peer slabs)' if slabs is not None else 'NCCL gather to rank 0'), l2='flushed between timed steps (256 MiB write)'),
-                    e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu)
+                                parallelism=f'one timelapse, timepoint shards x{world} (sharding.associate_sharded), ' + par,
+                                gathered_pairs_verified=gathered_pairs, l2='flushed between timed steps (256 MiB write)'),
+                    e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu, strong_c4=strong)
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -539,6 +632,8 @@ def main():
                     help="weak: the workload's T frames per GPU (default); strong: T frames in total, T/N per GPU")
     ap.add_argument('--gather', default='peer', choices=['peer', 'nccl'],
                     help='N > 1: K2 writes into rank 0 memory over NVLink (peer) or NCCL sends after the kernels (nccl)')
+    ap.add_argument('--no-strong-c4', dest='strong_c4', action='store_false',
+                    help='skip the strong_c4 sub-record (configs[3]: one 2000-frame timelapse over the N GPUs)')
     ap.add_argument('--max-px', type=int, default=500,
                     help='max_px_assoc_dist (SURVEY 8d: configs[2] is also swept at 1000; > 511 runs the wide all-levels kernel)')
     args = ap.parse_args()

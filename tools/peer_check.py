@@ -6,7 +6,7 @@ rank = int(os.environ['RANK']); world = int(os.environ['WORLD_SIZE']); local = i
 torch.cuda.set_device(local); dev = torch.device('cuda', local)
 dist.init_process_group('nccl', device_id=dev)
 wl = dict(bench.WORKLOADS['c2'], T=24)
-mask, Y, tt, t0 = bench.make_block(wl, 0)          # the same 24-frame timelapse on every rank
+mask, Y, tt, t0 = bench.make_block(wl)[:4]          # the same 24-frame timelapse on every rank
 Yd, td, md = torch.from_numpy(Y).to(dev), torch.from_numpy(tt).to(dev), torch.from_numpy(mask.astype(np.uint8)).to(dev)
 ref, _ = sharding.associate_sharded(Yd, td, md)
 slabs = sharding.PeerSlabs(dev, cap_elems=1000, cap_pairs=4)     # tiny: forces the collective growth path
