@@ -26,7 +26,8 @@ SYMBOLS = ('axb_create', 'axb_destroy', 'axb_last_error', 'axb_version', 'axb_la
            'axb_mask_words', 'axb_pack_mask', 'axb_pack_weights', 'axb_cost_matrix_batch',
            'axb_cost_matrix', 'axb_cost_matrix_batch_host', 'axb_cost_matrix_host',
            'axb_decode_nms', 'axb_decode_nms_host', 'axb_transition_cost_batch', 'axb_trace_paths', 'axb_feature_hist',
-           'axb_tile_nonempty', 'axb_gather_frametiles', 'axb_status')
+           'axb_feature_hist_frames', 'axb_vis_sim',
+           'axb_tile_nonempty', 'axb_gather_frametiles', 'axb_stitched_frame', 'axb_status')
 
 
 class PairDesc(ctypes.Structure):
@@ -89,10 +90,16 @@ def load():
     L.axb_transition_cost_batch.argtypes = [vp, vp, vp, ci, ci, vp, vp, ci, ci, vp, vp, vp]
     L.axb_feature_hist.restype = ci
     L.axb_feature_hist.argtypes = [vp, vp, ci, ci, vp, ci, ci, cf, cf, vp, vp]
+    L.axb_feature_hist_frames.restype = ci
+    L.axb_feature_hist_frames.argtypes = [vp, vp, ci, ci, ci, vp, vp, ci, ci, cf, cf, vp, vp]
+    L.axb_vis_sim.restype = ci
+    L.axb_vis_sim.argtypes = [vp, vp, ci, vp, ci, ci, vp, ci, vp, vp]
     L.axb_tile_nonempty.restype = ci
     L.axb_tile_nonempty.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp]
     L.axb_gather_frametiles.restype = ci
     L.axb_gather_frametiles.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, ci, vp, ci, ci, ci, ci, vp, vp]
+    L.axb_stitched_frame.restype = ci
+    L.axb_stitched_frame.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, ci, ci, ci, vp, vp]
     L.axb_status.restype = ci
     L.axb_status.argtypes = [vp, vp, ctypes.POINTER(ctypes.c_int64 * 3)]
     _lib = L

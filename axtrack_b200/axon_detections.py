@@ -15,7 +15,11 @@ astar_wrapper.py:35-45).  Use it on top of the reference's class:
     from axtrack.AxonDetections import AxonDetections as Ref
     class AxonDetections(B200AssociationMixin, Ref): pass          # or make_drop_in(Ref)
 
-Everything else (get_frame_dets, _assign_IDs_to_detections, libmot, ...) is inherited unchanged.
+    get_frame_and_truedets              AxonDetections.py:355-376 (the frame from the dense X, no tile round trip)
+    _assign_IDs_to_detections           AxonDetections.py:631-715 (unchanged code; only the tracker CLASS it builds is
+                                        swapped for libmot_bridge's, which adds the transition arcs from arrays)
+
+Everything else (get_frame_dets, libmot's solve, ...) is inherited unchanged.
 The mixin only touches: self.model.detect_axons, self.dataset.{name, mask, sizey, sizex, ytiles,
 xtiles, tile_info, construct_tiles, get_frametiles_stack}, self.{Sx, Sy, tilesize, nms_min_dist,
 all_conf_thrs, max_px_assoc_dist, MCF_max_num_misses, timepoint_subset, device, dir}.
@@ -209,11 +213,82 @@ class B200AssociationMixin:
             lbl = f'{name}_t:{t:0>3}-t:{tb:0>3}'
             dists[lbl] = pl[o:o + ns * nd].reshape(ns, nd).astype(np.int64)
             unreach[lbl] = un[o:o + ns * nd].reshape(ns, nd)
-        astar_dets_paths = AStarPaths(dists, unreach, masks.shape[1:])
+        if getattr(self, 'materialize_paths', False):
+            astar_dets_paths = self._materialize_paths(dists, unreach, keys, yx, masks, of_frame, bits)
+        else:
+            astar_dets_paths = AStarPaths(dists, unreach, masks.shape[1:])
         print('Done.')
         if cache == 'to':
             self.to_cache('astar_dets_paths', astar_dets_paths)
         return astar_dets_paths
+
+    def _materialize_paths(self, dists, unreach, keys, yx, masks, of_frame, bits, batch=32768):
+        """``materialize_paths = True``: the cache object exactly as the reference builds it (AxonDetections.py:578-579,
+        utils.py:381-384) -- a plain dict of nested lists whose leaves are ``scipy.sparse.coo_matrix(bool, (H, W))`` of
+        the path pixels or ``None`` -- so that the STOCK reference can ``from_cache('astar_dets_paths')`` it without
+        this package on its path.  The pixels come from K4 (``axb_trace_paths``): a minimum-cost path of exactly the
+        reference's length (which of the equal-cost paths is heap-order dependent in the reference)."""
+        from scipy.sparse import coo_matrix
+        name, shape = self.dataset.name, tuple(masks.shape[1:])
+        max_px = int(self.max_px_assoc_dist)
+        out, req, where = {}, [], []
+        for (t, tb) in keys:
+            lbl = f'{name}_t:{t:0>3}-t:{tb:0>3}'
+            un = unreach[lbl]
+            out[lbl] = [[None] * un.shape[1] for _ in range(un.shape[0])]
+            ii, jj = np.nonzero(un == 0)
+            for i, j in zip(ii.tolist(), jj.tolist()):
+                req.append((int(of_frame[t]), *yx[tb][i], *yx[t][j]))
+                where.append((lbl, i, j))
+        for b0 in range(0, len(req), batch):
+            r = np.asarray(req[b0:b0 + batch], np.int32).reshape(-1, 5)
+            pyx, ln = ops.trace_paths(bits, shape[1], r, max_px)
+            ops.raise_status(device=bits.device)
+            pyx, ln = pyx.cpu().numpy(), ln.cpu().numpy()
+            for k, (lbl, i, j) in enumerate(where[b0:b0 + batch]):
+                L = int(ln[k])
+                assert L == int(dists[lbl][i, j]), 'traced path and cost matrix disagree'
+                p = pyx[k, :L]
+                out[lbl][i][j] = coo_matrix((np.ones(L), (p[:, 0], p[:, 1])), shape, bool)      # utils.py:381-382
+        return out
+
+    # ---- get_frame_and_truedets: AxonDetections.py:355-376 ----------------------------------------------
+    def get_frame_and_truedets(self, t, unstitched=False):
+        """The stitched frame comes straight from the dense ``dataset.X`` (K6 ``axb_stitched_frame``: the frame with the
+        tiles that are empty at every timepoint zeroed) instead of tiles -> ``stitch_tiles``; the true detections
+        are the reference's (``stitch_tiles`` without an image).  ``unstitched=True`` and datasets without a dense
+        ``X`` take the reference's path."""
+        ds = self.dataset
+        if unstitched or getattr(ds, 'X', None) is None or not torch.cuda.is_available() or not getattr(self, 'frames_from_dense', True):
+            return super().get_frame_and_truedets(t, unstitched)
+        tiler = getattr(self, '_frame_tiler', None)
+        if tiler is None:
+            from .tiling import FrameTiler
+            dev = torch.device('cuda', torch.cuda.current_device())
+            X = ds.X.to_dense() if ds.X.is_sparse else ds.X
+            tiler = self._frame_tiler = FrameTiler(X.to(dev, torch.float32), ds.tilesize, ds.temporal_context,
+                                                   ds.use_motion_filtered, ds.timepoints_indices)
+        pd_tiled_true_det = self._yolo_Y2pandas_det(self._yolo_targets[t], conf_thr=1)
+        pd_frame_true_det, _ = ds.stitch_tiles(pd_tiled_true_det)
+        return tiler.stitched_frame(t).cpu(), pd_frame_true_det
+
+    # ---- _assign_IDs_to_detections: AxonDetections.py:631-715 ---------------------------------------------
+    def _assign_IDs_to_detections(self, cache=None):
+        """The reference's method, unchanged -- but the ``MinCostFlowTracker`` it instantiates (a module global of the
+        reference, AxonDetections.py:11,663) is libmot_bridge's subclass for the duration of the call: same nodes,
+        same ``AddArc...`` calls in the same order, the transition arcs taken from arrays (K3 / K7) instead of the
+        per-pair Python loop (offline_mincostflow.py:166-198).  ``arcs_from_arrays = False`` restores the loop."""
+        ref_fn = super()._assign_IDs_to_detections
+        if cache == 'from' or not getattr(self, 'arcs_from_arrays', True):
+            return ref_fn(cache)
+        from .libmot_bridge import make_arc_tracker
+        g = ref_fn.__func__.__globals__
+        Ref = g['MinCostFlowTracker']
+        g['MinCostFlowTracker'] = make_arc_tracker(Ref)
+        try:
+            return ref_fn(cache)
+        finally:
+            g['MinCostFlowTracker'] = Ref
 
     # ---- _get_astar_path_distances: AxonDetections.py:717-752 ---------------------------------------
     def _get_astar_path_distances(self, astar_paths):

@@ -3,6 +3,7 @@
 #include "axb_common.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -14,6 +15,11 @@ struct axb_ctx {
     std::string err;
     int64_t launches = 0;
     cudaStream_t own_stream = nullptr;
+    // chunked host entry (axb_cost_matrix_batch_host): a second scratch set + stream so that the searches of chunk
+    // k+1 fill the SMs while chunk k drains, and a copy stream that takes finished chunks to the host meanwhile
+    axb_ctx* alt = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_chunk[2] = {nullptr, nullptr};
 
     // device-side sticky status: [0] first input error key (atomicMin), [1] flag bits (atomicOr)
     unsigned long long* status_dev = nullptr;
@@ -141,6 +147,10 @@ void axb_destroy(axb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+    if (c->alt) { axb_destroy(c->alt); c->alt = nullptr; }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->ev_in) cudaEventDestroy(c->ev_in);
+    for (int i = 0; i < 2; ++i) if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_fast_scratch); cudaFree(c->k2_pool_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
     cudaFree(c->trace_par); cudaFree(c->trace_iota); cudaFree(c->k2_wide_scratch); cudaFree(c->trace_par_wide);
@@ -177,11 +187,49 @@ int axb_pack_weights(axb_ctx* c, const float* weights_dev, int n_masks, int H, i
     return AXB_OK;
 }
 
-int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
-                          const int32_t* dets_yx_dev, int n_dets, const axb_pair_desc* pairs_dev, int n_pairs,
-                          int total_src, int max_px,
-                          int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, int64_t out_capacity,
-                          void* stream) {
+}  // extern "C"
+
+namespace {
+// Device-side sticky status -> host, cleared.  Synchronises `s`.
+int status_fetch(axb_ctx* c, cudaStream_t s, unsigned long long* key, unsigned long long* flags) {
+    AXB_CUDA(c, cudaMemcpyAsync(c->status_host, c->status_dev, 16, cudaMemcpyDeviceToHost, s));
+    AXB_CUDA(c, cudaStreamSynchronize(s));
+    *key = c->status_host[0]; *flags = c->status_host[1];
+    if (*key != ~0ull || *flags) {
+        c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
+        AXB_CUDA(c, cudaMemcpyAsync(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice, s));
+        AXB_CUDA(c, cudaStreamSynchronize(s));
+    }
+    return AXB_OK;
+}
+
+// (key, flags) -> return code; for an out-of-grid end point info = (pair, source, target), the work item of the key
+// mapped to its pair by `locate(item, &pair, &source)`.
+template <class Locate>
+int status_decode(axb_ctx* c, unsigned long long key, unsigned long long flags, int64_t info[3], Locate locate) {
+    if (info) { info[0] = info[1] = info[2] = -1; }
+    int rc = AXB_OK;
+    if (flags & 1ull) rc = AXB_ERR_BAD_WEIGHT;                       // checked first by the reference (astar_wrapper.py:35)
+    else if (key != ~0ull) {
+        const int code = (int)(key & 3ull);
+        const long long j = (long long)((key >> 2) & 0xFFFFFFull);
+        const long long item = (long long)(key >> 26);
+        rc = code == 1 ? AXB_ERR_OOB_START : AXB_ERR_OOB_GOAL;
+        if (info) { info[2] = j; info[0] = -1; info[1] = item; locate(item, &info[0], &info[1]); }
+    }
+    else if (flags & 2ull) rc = AXB_ERR_UNSUPPORTED_WEIGHT;
+    else if (flags & 4ull) rc = AXB_ERR_CAPACITY;
+    else if (flags & 8ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_transition_cost_batch: path length or time gap outside its table"; }
+    else if (flags & 16ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_gather_frametiles: a frame's temporal context leaves the timelapse"; }
+    else if (flags & 32ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_cost_matrix_batch: a pair descriptor points outside the detections / masks / outputs, or total_src is smaller than the pairs' sources"; }
+    return rc;
+}
+
+int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
+                           const int32_t* dets_yx_dev, int n_dets, const axb_pair_desc* pairs_dev, int n_pairs,
+                           int total_src, int max_px,
+                           int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, int64_t out_capacity,
+                           long long orig_base, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (n_pairs < 0 || total_src < 0 || H <= 0 || W <= 0 || n_masks <= 0 || n_dets < 0 || out_capacity < 0)
         return bad_arg(c, "axb_cost_matrix_batch: bad size");
@@ -216,6 +264,7 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     p.pool_scratch = c->k2_pool_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
+    p.orig_base = orig_base;
     if (wide) {      // beyond the tile-word kernels' window: every source goes through the wide all-levels kernel
         axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
         axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * axb::kWideCtasPerSm, total_src)), s);
@@ -236,6 +285,19 @@ int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks
     c->launches += 5;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
+                          const int32_t* dets_yx_dev, int n_dets, const axb_pair_desc* pairs_dev, int n_pairs,
+                          int total_src, int max_px,
+                          int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, int64_t out_capacity,
+                          void* stream) {
+    return cost_matrix_batch_impl(c, mask_bits_dev, n_masks, H, W, dets_yx_dev, n_dets, pairs_dev, n_pairs, total_src, max_px,
+                                  path_len_dev, unreachable_dev, wcost_dev, out_capacity, 0, stream);
 }
 
 int axb_cost_matrix(axb_ctx* c, const uint32_t* mask_bits_dev, int H, int W,
@@ -272,6 +334,7 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
     if (!masks_host || !pairs_host || !path_len_host || !unreachable_host || (n_dets > 0 && !dets_yx_host))
         return bad_arg(c, "axb_cost_matrix_batch_host: NULL pointer");
     long long total_out = 0; long long total_src = 0;
+    std::vector<long long> src_prefix((size_t)n_pairs + 1, 0);
     for (int i = 0; i < n_pairs; ++i) {
         const axb_pair_desc& pd = pairs_host[i];
         if (pd.n_src < 0 || pd.n_dst < 0 || pd.src_off < 0 || pd.dst_off < 0 || pd.src_off + pd.n_src > n_dets ||
@@ -279,6 +342,7 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
             return bad_arg(c, "axb_cost_matrix_batch_host: pair descriptor out of range");
         total_out = std::max(total_out, (long long)pd.out_off + (long long)pd.n_src * pd.n_dst);
         total_src += pd.n_src;
+        src_prefix[(size_t)i + 1] = total_src;
     }
     if (total_src > 0x7fffffffLL) return bad_arg(c, "axb_cost_matrix_batch_host: too many sources");
     AXB_ON_DEVICE(c);
@@ -297,16 +361,76 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
     if (n_dets > 0) AXB_CUDA(c, cudaMemcpyAsync(c->st_dets, dets_yx_host, (size_t)n_dets * 8, cudaMemcpyHostToDevice, s));
     AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, pairs_host, (size_t)n_pairs * sizeof(axb_pair_desc), cudaMemcpyHostToDevice, s));
     if ((rc = axb_pack_mask(c, c->st_mask, n_masks, H, W, c->st_bits, s)) != AXB_OK) return rc;
-    if (total_out > 0 && total_src > 0) {
-        rc = axb_cost_matrix_batch(c, c->st_bits, n_masks, H, W, c->st_dets, n_dets, c->st_pairs, n_pairs, (int)total_src,
-                                   max_px, c->st_plen, c->st_unr, wcost_host ? c->st_wc : nullptr, (int64_t)total_out, s);
-        if (rc != AXB_OK) return rc;
-        AXB_CUDA(c, cudaMemcpyAsync(path_len_host, c->st_plen, (size_t)total_out * 4, cudaMemcpyDeviceToHost, s));
-        AXB_CUDA(c, cudaMemcpyAsync(unreachable_host, c->st_unr, (size_t)total_out, cudaMemcpyDeviceToHost, s));
-        if (wcost_host) AXB_CUDA(c, cudaMemcpyAsync(wcost_host, c->st_wc, (size_t)total_out * 4, cudaMemcpyDeviceToHost, s));
+
+    // Chunks of frame pairs: the searches of chunk k+1 (other scratch set, other stream) fill the SMs as chunk k
+    // drains, and the copy stream takes chunk k's matrices to the host meanwhile.  Every chunk costs a launch-group
+    // tail (~1 ms) and the last chunk's copy is exposed, so n ~ sqrt(copy time / tail): one chunk up to ~100 MB of
+    // results (configs[1]: 44 MB, measured faster unchunked), 5 for the 1.36 GB of configs[2]; a chunk holds at least
+    // four full rounds of searches.
+    static const bool no_chunks = getenv("AXB_HOST_NO_CHUNKS") != nullptr;
+    const double out_mb = (double)total_out * (wcost_host ? 9.0 : 5.0) / (1 << 20);
+    int n_chunks = (int)std::min<long long>(std::min<long long>(8, (long long)(std::sqrt(out_mb / 64.0) + 0.5)),
+                                            total_src / (4LL * c->num_sms * axb::kSparseCtasPerSm));
+    if (n_chunks < 2 || no_chunks || total_out <= 0) n_chunks = 1;
+    axb_ctx* ctxs[2] = {c, c};
+    if (n_chunks > 1) {
+        if (!c->alt && (rc = axb_create(c->device, &c->alt)) != AXB_OK) return rc;
+        if (!c->copy_stream) AXB_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        if (!c->ev_in) AXB_CUDA(c, cudaEventCreateWithFlags(&c->ev_in, cudaEventDisableTiming));
+        for (int i = 0; i < 2; ++i)
+            if (!c->ev_chunk[i]) AXB_CUDA(c, cudaEventCreateWithFlags(&c->ev_chunk[i], cudaEventDisableTiming));
+        ctxs[1] = c->alt;
+        AXB_CUDA(c, cudaEventRecord(c->ev_in, s));
+        AXB_CUDA(c, cudaStreamWaitEvent(c->alt->own_stream, c->ev_in, 0));
     }
+    if (total_out > 0 && total_src > 0) {
+        int p0 = 0;
+        for (int k = 0; k < n_chunks; ++k) {
+            int p1 = n_pairs;
+            if (k + 1 < n_chunks) {            // cut where the running source count passes k+1 shares
+                const long long want = total_src * (k + 1) / n_chunks;
+                p1 = (int)(std::lower_bound(src_prefix.begin(), src_prefix.end(), want) - src_prefix.begin());
+                p1 = std::min(std::max(p1, p0), n_pairs);
+            }
+            if (p1 == p0) continue;
+            axb_ctx* const cc = ctxs[k & 1];
+            cudaStream_t cs = cc->own_stream;
+            rc = cost_matrix_batch_impl(cc, c->st_bits, n_masks, H, W, c->st_dets, n_dets, c->st_pairs + p0, p1 - p0,
+                                        (int)(src_prefix[p1] - src_prefix[p0]), max_px, c->st_plen, c->st_unr,
+                                        wcost_host ? c->st_wc : nullptr, (int64_t)total_out, src_prefix[p0], cs);
+            if (rc != AXB_OK) { if (cc != c) c->err = cc->err; return rc; }
+            long long lo = total_out, hi = 0;
+            for (int i = p0; i < p1; ++i) {
+                lo = std::min(lo, (long long)pairs_host[i].out_off);
+                hi = std::max(hi, (long long)pairs_host[i].out_off + (long long)pairs_host[i].n_src * pairs_host[i].n_dst);
+            }
+            cudaStream_t ds = cs;
+            if (n_chunks > 1) {
+                AXB_CUDA(c, cudaEventRecord(c->ev_chunk[k & 1], cs));
+                AXB_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_chunk[k & 1], 0));
+                ds = c->copy_stream;
+            }
+            if (hi > lo) {
+                AXB_CUDA(c, cudaMemcpyAsync(path_len_host + lo, c->st_plen + lo, (size_t)(hi - lo) * 4, cudaMemcpyDeviceToHost, ds));
+                AXB_CUDA(c, cudaMemcpyAsync(unreachable_host + lo, c->st_unr + lo, (size_t)(hi - lo), cudaMemcpyDeviceToHost, ds));
+                if (wcost_host) AXB_CUDA(c, cudaMemcpyAsync(wcost_host + lo, c->st_wc + lo, (size_t)(hi - lo) * 4, cudaMemcpyDeviceToHost, ds));
+            }
+            p0 = p1;
+        }
+    }
+    // status of both scratch sets: the first error in the reference's iteration order (the keys are global)
+    unsigned long long key = ~0ull, flags = 0ull;
+    for (int i = 0; i < (n_chunks > 1 ? 2 : 1); ++i) {
+        unsigned long long k2 = ~0ull, f2 = 0ull;
+        if ((rc = status_fetch(ctxs[i], ctxs[i]->own_stream, &k2, &f2)) != AXB_OK) return rc;
+        key = std::min(key, k2); flags |= f2;
+    }
+    if (n_chunks > 1) AXB_CUDA(c, cudaStreamSynchronize(c->copy_stream));
     int64_t info[3];
-    rc = axb_status(c, s, info);       // synchronises
+    rc = status_decode(c, key, flags, info, [&](long long item, int64_t* pair, int64_t* src) {
+        const int lo = (int)(std::upper_bound(src_prefix.begin(), src_prefix.begin() + n_pairs, item) - src_prefix.begin()) - 1;
+        *pair = std::max(lo, 0); *src = item - src_prefix[std::max(lo, 0)];
+    });
     if ((rc == AXB_ERR_OOB_START || rc == AXB_ERR_OOB_GOAL) && info[0] >= 0 && info[0] < n_pairs) {
         // the reference's message (astar_wrapper.py:41,45)
         const axb_pair_desc& pd = pairs_host[info[0]];
@@ -468,15 +592,33 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     return AXB_OK;
 }
 
-int axb_feature_hist(axb_ctx* c, const float* image_dev, int H, int W, const int32_t* boxes_dev, int n_boxes,
-                     int bins, float lo, float hi, float* out_dev, void* stream) {
+int axb_feature_hist_frames(axb_ctx* c, const float* images_dev, int n_frames, int H, int W, const int32_t* boxes_dev,
+                            const int32_t* box_frame_dev, int n_boxes, int bins, float lo, float hi, float* out_dev, void* stream) {
     if (!c) return AXB_ERR_BAD_ARG;
-    if (H <= 0 || W <= 0 || n_boxes < 0 || bins < 1 || bins > AXB_MAX_BINS || !(hi > lo))
+    if (H <= 0 || W <= 0 || n_frames < 1 || n_boxes < 0 || bins < 1 || bins > AXB_MAX_BINS || !(hi > lo))
         return bad_arg(c, "axb_feature_hist: bad size, bins outside [1, AXB_MAX_BINS] or empty range");
     if (n_boxes == 0) return AXB_OK;
-    if (!image_dev || !boxes_dev || !out_dev) return bad_arg(c, "axb_feature_hist: NULL pointer");
+    if (!images_dev || !boxes_dev || !out_dev) return bad_arg(c, "axb_feature_hist: NULL pointer");
     AXB_ON_DEVICE(c);
-    axb::launch_k5(image_dev, H, W, boxes_dev, n_boxes, bins, lo, hi, out_dev, (cudaStream_t)stream);
+    axb::launch_k5(images_dev, n_frames, H, W, boxes_dev, box_frame_dev, n_boxes, bins, lo, hi, out_dev, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
+int axb_feature_hist(axb_ctx* c, const float* image_dev, int H, int W, const int32_t* boxes_dev, int n_boxes,
+                     int bins, float lo, float hi, float* out_dev, void* stream) {
+    return axb_feature_hist_frames(c, image_dev, 1, H, W, boxes_dev, nullptr, n_boxes, bins, lo, hi, out_dev, stream);
+}
+
+int axb_vis_sim(axb_ctx* c, const float* feats_src_dev, int n_src, const float* feats_dst_dev, int n_dst, int bins,
+                const int32_t* path_len_dev, int max_px, double* vis_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (n_src < 0 || n_dst < 0 || bins < 1 || bins > AXB_MAX_BINS) return bad_arg(c, "axb_vis_sim: bad size or bins outside [1, AXB_MAX_BINS]");
+    if (n_src == 0 || n_dst == 0) return AXB_OK;
+    if (!feats_src_dev || !feats_dst_dev || !vis_dev) return bad_arg(c, "axb_vis_sim: NULL pointer");
+    AXB_ON_DEVICE(c);
+    axb::launch_k7(feats_src_dev, n_src, feats_dst_dev, n_dst, bins, path_len_dev, max_px, vis_dev, (cudaStream_t)stream);
     c->launches += 1;
     AXB_CUDA(c, cudaGetLastError());
     return AXB_OK;
@@ -533,44 +675,35 @@ int axb_gather_frametiles(axb_ctx* c, const float* X_dev, int T, int C, int H, i
     return AXB_OK;
 }
 
+int axb_stitched_frame(axb_ctx* c, const float* X_dev, int T, int C, int H, int W, int tilesize, const uint8_t* tile_keep_dev,
+                       int frame, int chan_lo, int chan_n, float* out_dev, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (T <= 0 || C < 1 || H <= 0 || W <= 0 || tilesize < 1 || frame < 0 || frame >= T) return bad_arg(c, "axb_stitched_frame: bad size or frame outside [0, T)");
+    if (chan_lo < 0 || chan_n < 1 || chan_lo + chan_n > C) return bad_arg(c, "axb_stitched_frame: channel range outside [0, C)");
+    if (!X_dev || !tile_keep_dev || !out_dev) return bad_arg(c, "axb_stitched_frame: NULL pointer");
+    AXB_ON_DEVICE(c);
+    axb::launch_k6_frame(X_dev, C, H, W, tilesize, tile_keep_dev, frame, chan_lo, chan_n, out_dev, c->num_sms, (cudaStream_t)stream);
+    c->launches += 1;
+    AXB_CUDA(c, cudaGetLastError());
+    return AXB_OK;
+}
+
 int axb_status(axb_ctx* c, void* stream, int64_t info[3]) {
     if (!c) return AXB_ERR_BAD_ARG;
     AXB_ON_DEVICE(c);
-    cudaStream_t s = (cudaStream_t)stream;
-    AXB_CUDA(c, cudaMemcpyAsync(c->status_host, c->status_dev, 16, cudaMemcpyDeviceToHost, s));
-    AXB_CUDA(c, cudaStreamSynchronize(s));
-    const unsigned long long key = c->status_host[0], flags = c->status_host[1];
-    if (info) { info[0] = info[1] = info[2] = -1; }
-    int rc = AXB_OK;
-    if (flags & 1ull) rc = AXB_ERR_BAD_WEIGHT;                       // checked first by the reference (astar_wrapper.py:35)
-    else if (key != ~0ull) {
-        const int code = (int)(key & 3ull);
-        const long long j = (long long)((key >> 2) & 0xFFFFFFull);
-        const long long item = (long long)(key >> 26);
-        rc = code == 1 ? AXB_ERR_OOB_START : AXB_ERR_OOB_GOAL;
-        if (info) {
-            info[2] = j; info[0] = -1; info[1] = item;
-            const int n = c->last_n_pairs;
-            if (n > 0 && c->prefix_dev) {
-                std::vector<int> pre((size_t)n + 1);
-                AXB_CUDA(c, cudaMemcpy(pre.data(), c->prefix_dev + c->prefix_cap, ((size_t)n + 1) * sizeof(int), cudaMemcpyDeviceToHost));
-                int lo = (int)(std::upper_bound(pre.begin(), pre.begin() + n, (int)item) - pre.begin()) - 1;
-                lo = std::max(lo, 0);
-                info[0] = lo; info[1] = item - pre[lo];
-            }
-        }
-    }
-    else if (flags & 2ull) rc = AXB_ERR_UNSUPPORTED_WEIGHT;
-    else if (flags & 4ull) rc = AXB_ERR_CAPACITY;
-    else if (flags & 8ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_transition_cost_batch: path length or time gap outside its table"; }
-    else if (flags & 16ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_gather_frametiles: a frame's temporal context leaves the timelapse"; }
-    else if (flags & 32ull) { rc = AXB_ERR_BAD_ARG; c->err = "axb_cost_matrix_batch: a pair descriptor points outside the detections / masks / outputs, or total_src is smaller than the pairs' sources"; }
-    if (key != ~0ull || flags) {
-        c->status_host[0] = ~0ull; c->status_host[1] = 0ull;
-        AXB_CUDA(c, cudaMemcpyAsync(c->status_dev, c->status_host, 16, cudaMemcpyHostToDevice, s));
-        AXB_CUDA(c, cudaStreamSynchronize(s));
-    }
-    return rc;
+    unsigned long long key = ~0ull, flags = 0ull;
+    int rc = status_fetch(c, (cudaStream_t)stream, &key, &flags);
+    if (rc != AXB_OK) return rc;
+    std::vector<int> pre;
+    return status_decode(c, key, flags, info, [&](long long item, int64_t* pair, int64_t* src) {
+        const int n = c->last_n_pairs;
+        if (n <= 0 || !c->prefix_dev) return;
+        pre.resize((size_t)n + 1);
+        if (cudaMemcpy(pre.data(), c->prefix_dev + c->prefix_cap, ((size_t)n + 1) * sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+        int lo = (int)(std::upper_bound(pre.begin(), pre.begin() + n, (int)item) - pre.begin()) - 1;
+        lo = std::max(lo, 0);
+        *pair = lo; *src = item - pre[lo];
+    });
 }
 
 }  // extern "C"

@@ -90,6 +90,7 @@ struct K2Params {
     int32_t* trace_yx;           // [n_pairs][max_px][2] (row, col), start -> goal
     int32_t* trace_len;          // [n_pairs] pixels on the path, 0 = None
     unsigned long long* err_key; // atomicMin: (item in reference order << 26 | target << 2 | code)
+    long long orig_base;         // sources of the pairs that precede this call's pairs in the caller's batch (chunked host entry)
 };
 
 inline int k2_tile_rows(int max_px) { return (max_px + 3) / 4 + 1; }
@@ -145,14 +146,19 @@ void launch_k3(const int32_t* path_len, const axb_pair_desc* pairs, int n_pairs,
                const long long* arc_tab, int n_gaps, int max_px, double* cost, long long* arc,
                unsigned long long* err_flags, int max_elems_per_pair, cudaStream_t stream);
 
-void launch_k5(const float* image, int H, int W, const int32_t* boxes, int n_boxes, int bins, float lo, float hi,
-               float* out, cudaStream_t stream);
+void launch_k5(const float* images, int n_frames, int H, int W, const int32_t* boxes, const int32_t* box_frame, int n_boxes,
+               int bins, float lo, float hi, float* out, cudaStream_t stream);
+void launch_k7(const float* f_src, int n_src, const float* f_dst, int n_dst, int bins, const int32_t* path_len, int max_px,
+               double* vis, cudaStream_t stream);
 
 constexpr int kK6FlagStride = 8;      // uint32 words between two K6 vote flags: one flag per 32-byte sector
 void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint32_t* flags, uint8_t* nonempty, cudaStream_t stream);
 void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,
                       const int32_t* frames, int B, int tc, int chan_lo, int nch, float* out,
                       unsigned long long* err_flags, int n_sms, cudaStream_t stream);
+
+void launch_k6_frame(const float* X, int C, int H, int W, int ts, const uint8_t* keep, int frame, int chan_lo, int nch,
+                     float* out, int n_sms, cudaStream_t stream);
 
 // ---- K1 ------------------------------------------------------------------------------------
 struct K1Params {

@@ -145,7 +145,7 @@ __device__ bool setup_slot(const K2Params& p, const PoolMem& m, PoolCtl& ctl, co
             while (q >= 0 && nm < kMaxChain) {
                 const axb_pair_desc pd = p.pairs[q];
                 ch.orow[nm] = pd.out_off + (long long)si * pd.n_dst;
-                ch.item_orig[nm] = (long long)p.all_prefix[q] + si;
+                ch.item_orig[nm] = p.orig_base + (long long)p.all_prefix[q] + si;
                 ch.dst_off[nm] = pd.dst_off;
                 ch.cum[nm + 1] = ch.cum[nm] + max(pd.n_dst, 0);
                 ++nm;

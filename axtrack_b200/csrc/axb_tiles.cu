@@ -106,6 +106,30 @@ __global__ void __launch_bounds__(256) k6_gather_kernel(const float* __restrict_
     }
 }
 
+// The frame a tracker draws its crops from (AxonDetections.get_frame_and_truedets, AxonDetections.py:355-376 ->
+// Timelapse.stitch_tiles image half, Timelapse.py:173-188): the reference cuts the frame into tiles, drops the
+// tiles that are empty at every timepoint and stitches the rest back -- i.e. the dense frame with the dropped
+// tiles zeroed.  Here: one pass over the dense X, out[ch][y][x] = keep[tile(y, x)] ? X[frame][chan_lo + ch][y][x] : 0.
+__global__ void __launch_bounds__(256) k6_frame_kernel(const float* __restrict__ X, int C, int H, int W, int ts, int xtiles,
+                                                       const uint8_t* __restrict__ keep, int frame, int chan_lo, int nch,
+                                                       float* __restrict__ out) {
+    const size_t n = (size_t)nch * H * W;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int x = (int)(i % W);
+        const size_t r = i / W;
+        const int y = (int)(r % H), ch = (int)(r / H);
+        const bool k = keep[(y / ts) * xtiles + x / ts] != 0;
+        out[i] = k ? __ldg(X + (((size_t)frame * C + chan_lo + ch) * H + y) * W + x) : 0.0f;
+    }
+}
+
+void launch_k6_frame(const float* X, int C, int H, int W, int ts, const uint8_t* keep, int frame, int chan_lo, int nch,
+                     float* out, int n_sms, cudaStream_t stream) {
+    const size_t n = (size_t)nch * H * W;
+    const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)n_sms * 16);
+    k6_frame_kernel<<<grid > 0 ? grid : 1, 256, 0, stream>>>(X, C, H, W, ts, (W + ts - 1) / ts, keep, frame, chan_lo, nch, out);
+}
+
 void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint32_t* flags, uint8_t* nonempty, cudaStream_t stream) {
     const int ytiles = (H + ts - 1) / ts, xtiles = (W + ts - 1) / ts;
     const size_t n = (size_t)ytiles * xtiles * T;

@@ -269,6 +269,46 @@ def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
     return out
 
 
+def feature_hist_frames(images, boxes, box_frame, bins=180, lo=0.0, hi=1.0):
+    """K5 for the boxes of a BLOCK of frames in one launch: images float32 CUDA [F, H, W]; boxes int32
+    CUDA [n, 4] rows (x, y, w, h); box_frame int32 CUDA [n] = frame of each box.  -> float32 CUDA [n, bins]."""
+    images = _need_cuda(images, 'images', torch.float32)
+    assert images.dim() == 3, 'images must be [F, H, W]'
+    boxes = _need_cuda(boxes.reshape(-1, 4), 'boxes', torch.int32)
+    box_frame = _need_cuda(box_frame.reshape(-1), 'box_frame', torch.int32)
+    n = boxes.shape[0]
+    assert box_frame.shape[0] == n
+    dev = images.device
+    ctx = get_context(dev)
+    out = torch.empty((n, int(bins)), dtype=torch.float32, device=dev)
+    if n:
+        F, H, W = images.shape
+        ctx.check(ctx.lib.axb_feature_hist_frames(ctx.handle, images.data_ptr(), int(F), int(H), int(W), boxes.data_ptr(),
+                                                  box_frame.data_ptr(), n, int(bins), float(lo), float(hi), out.data_ptr(), _stream(dev)))
+    return out
+
+
+def vis_sim(feats_src, feats_dst, path_len=None, max_px=500):
+    """K7: ``nan_to_num(1 - cv2.compareHist(f1, f2, HISTCMP_BHATTACHARYYA))`` for every (predecessor, current)
+    pair of feature histograms (mincostflow_models.py:106-113), bit-identical to cv2 4.13.
+
+    feats_* float32 CUDA [n, bins] (or [n, bins, 1] as feature_model returns them); path_len optional int32 CUDA
+    [n_src, n_dst]: entries equal to max_px are skipped (their cost is inf anyway).  -> float64 CUDA [n_src, n_dst]."""
+    fs = _need_cuda(feats_src.reshape(feats_src.shape[0], -1), 'feats_src', torch.float32)
+    fd = _need_cuda(feats_dst.reshape(feats_dst.shape[0], -1), 'feats_dst', torch.float32)
+    assert fs.shape[1] == fd.shape[1]
+    ns, nd, bins = fs.shape[0], fd.shape[0], fs.shape[1]
+    dev = fs.device
+    ctx = get_context(dev)
+    vis = torch.zeros((ns, nd), dtype=torch.float64, device=dev)
+    if path_len is not None:
+        path_len = _need_cuda(path_len.reshape(ns, nd), 'path_len', torch.int32)
+    if ns and nd:
+        ctx.check(ctx.lib.axb_vis_sim(ctx.handle, fs.data_ptr(), ns, fd.data_ptr(), nd, int(bins),
+                                      path_len.data_ptr() if path_len is not None else None, int(max_px), vis.data_ptr(), _stream(dev)))
+    return vis
+
+
 #: USE_MOTION_DATA -> (first channel, number of channels) of X (Timelapse.py:116-124, 415-424)
 MOTION_CHANNELS = {'exclude': (0, 1), 'temp_context': (0, 1), 'only': (1, 2), 'include': (0, 3)}
 
@@ -317,4 +357,22 @@ def gather_frametiles(X, tile_yx, frames, tilesize=512, temporal_context=2, use_
     ctx.check(ctx.lib.axb_gather_frametiles(ctx.handle, X.data_ptr(), int(T), int(C), int(H), int(W), int(tilesize),
                                             tile_yx.data_ptr(), int(nt), frames.data_ptr(), int(B),
                                             int(temporal_context), int(lo), int(nch), out.data_ptr(), _stream(X.device)))
+    return out
+
+
+def stitched_frame(X, nonempty, frame, tilesize=512, use_motion_filtered='exclude'):
+    """The frame of AxonDetections.get_frame_and_truedets(t)[0] (AxonDetections.py:355-376) straight from the dense
+    timelapse: X float32 CUDA [T, C, H, W]; nonempty bool CUDA [ytiles, xtiles, T] (``tile_nonempty``); frame = raw
+    frame index.  -> float32 CUDA [nch, H, W]: the frame with the tiles that are empty at every t zeroed, which is
+    what Timelapse.stitch_tiles (Timelapse.py:173-188) rebuilds from the kept tiles."""
+    X = _need_cuda(X, 'X', torch.float32)
+    T, C, H, W = X.shape
+    keep = nonempty.any(-1).to(torch.uint8).contiguous()
+    lo, nch = MOTION_CHANNELS[use_motion_filtered]
+    if use_motion_filtered == 'temp_context':
+        raise ValueError("Timelapse._get_channelsizes has no 'temp_context' branch (Timelapse.py:415-424)")
+    ctx = get_context(X.device)
+    out = torch.empty((nch, H, W), dtype=torch.float32, device=X.device)
+    ctx.check(ctx.lib.axb_stitched_frame(ctx.handle, X.data_ptr(), int(T), int(C), int(H), int(W), int(tilesize), keep.data_ptr(),
+                                         int(frame), int(lo), int(nch), out.data_ptr(), _stream(X.device)))
     return out

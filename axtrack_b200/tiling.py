@@ -47,6 +47,11 @@ class FrameTiler:
         """The X of Timelapse.get_frametiles_stack(timepoint): [ntiles, nchnls, ts, ts]."""
         return self.get_frametiles_batch([timepoint])[0]
 
+    def stitched_frame(self, timepoint):
+        """AxonDetections.get_frame_and_truedets(timepoint)[0]: float32 CUDA [nch, H, W] (no tile round trip)."""
+        return ops.stitched_frame(self.X, self.nonempty, self.timepoints_indices[int(timepoint)], self.tilesize,
+                                  self.use_motion_filtered)
+
     def detect_frames(self, model, timepoints, frames_per_forward=8):
         """Head tensors [B, ntiles, Sx, Sy, 3] of the timepoints: ``model.detect_axons`` on
         ``frames_per_forward`` frames per forward (all their tiles as one batch)."""

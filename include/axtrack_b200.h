@@ -203,6 +203,23 @@ int axb_trace_paths(axb_ctx* ctx, const uint32_t* mask_bits_dev, int n_masks, in
 int axb_feature_hist(axb_ctx* ctx, const float* image_dev, int H, int W,
                      const int32_t* boxes_dev, int n_boxes, int bins, float lo, float hi,
                      float* out_dev, void* stream);
+/* The same for the boxes of a BLOCK of frames in one launch (libmot calls feature_model once per frame,
+ * offline_mincostflow.py:130; the frames of a timelapse are known up front): images_dev float32
+ * [n_frames][H][W], box_frame_dev int32 [n_boxes] = frame of each box (NULL: all on frame 0). */
+int axb_feature_hist_frames(axb_ctx* ctx, const float* images_dev, int n_frames, int H, int W,
+                            const int32_t* boxes_dev, const int32_t* box_frame_dev, int n_boxes,
+                            int bins, float lo, float hi, float* out_dev, void* stream);
+
+/* ---- visual similarity (the vis_sim term of transition_model) ------------------
+ * Replaces the double loop mincostflow_models.py:106-113 over (predecessor, current) detections:
+ *   vis[i][j] = nan_to_num(1 - cv2.compareHist(f_src[i], f_dst[j], cv2.HISTCMP_BHATTACHARYYA))
+ * feats_*_dev float32 [n][bins] (axb_feature_hist output); vis_dev float64 [n_src][n_dst].  The sums
+ * follow OpenCV 4.x's baseline (SSE) order in double, so the result is bit-identical to cv2 4.13.
+ * path_len_dev (optional int32 [n_src][n_dst], the A* distances of the same frame pair): entries equal
+ * to max_px are skipped and written as 0 -- transition_model overwrites their cost with inf
+ * (mincostflow_models.py:104,118), so the similarity never reaches the solver. */
+int axb_vis_sim(axb_ctx* ctx, const float* feats_src_dev, int n_src, const float* feats_dst_dev, int n_dst,
+                int bins, const int32_t* path_len_dev, int max_px, double* vis_dev, void* stream);
 
 /* ---- tiling front end of the detector --------------------------------------
  * X_dev float32 [T][C][H][W]: the dense timelapse (Timelapse.X.to_dense(), Timelapse.py:426-433:
@@ -226,6 +243,15 @@ int axb_tile_nonempty(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int
 int axb_gather_frametiles(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
                           const int32_t* tile_yx_dev, int ntiles, const int32_t* frames_dev, int n_frames,
                           int temporal_context, int chan_lo, int chan_n, float* out_dev, void* stream);
+
+/* The frame a tracker crops its feature boxes from: AxonDetections.get_frame_and_truedets(t)[0]
+ * (AxonDetections.py:355-376), which the reference obtains by tiling the frame and stitching the non-empty
+ * tiles back (Timelapse.stitch_tiles image half, Timelapse.py:173-188) = the dense frame with the tiles that
+ * are empty at every timepoint zeroed.  tile_keep_dev uint8 [ytiles * xtiles] (1 = kept: non-empty at any t,
+ * Timelapse.py:558); frame = raw frame index; out_dev float32 [chan_n][H][W]. */
+int axb_stitched_frame(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
+                       const uint8_t* tile_keep_dev, int frame, int chan_lo, int chan_n,
+                       float* out_dev, void* stream);
 
 /* ---- transition costs ------------------------------------------------------------------
  * Replaces the arithmetic of mincostflow_models.transition_model (mincostflow_models.py:100-119)

@@ -311,6 +311,37 @@ def transition_cost(path_len, max_px=500, miss_rate=0.6, time_gap=1, vis_sim_wei
     return costs
 
 
+def bhattacharyya(h1, h2):
+    """cv2.compareHist(h1, h2, cv2.HISTCMP_BHATTACHARYYA) for float32 histograms, restated: OpenCV 4.x sums
+    s1 = sum h1, s2 = sum h2, r = sum sqrt(h1*h2) in double in the order of its baseline SSE build (four floats
+    per step: the low pair then the high pair added to a two-lane accumulator, lanes added 0 + lane0 + lane1, the
+    len % 4 tail one by one) and returns sqrt(max(1 - r / sqrt(s1*s2), 0)), with 1 / sqrt(s1*s2) := 1 when
+    |s1*s2| <= FLT_EPSILON.  Pinned bit for bit against cv2 4.13 (tests/test_vis_sim.py)."""
+    a = np.asarray(h1, np.float32).reshape(-1).astype(np.float64)
+    b = np.asarray(h2, np.float32).reshape(-1).astype(np.float64)
+    n = len(a)
+    body = n & ~3
+
+    def lanes(v):
+        l0 = l1 = 0.0
+        for k in range(0, body, 2):
+            l0 += float(v[k]); l1 += float(v[k + 1])
+        t = (0.0 + l0) + l1
+        for k in range(body, n):
+            t += float(v[k])
+        return t
+    r, s1, s2 = lanes(np.sqrt(a * b)), lanes(a), lanes(b)
+    s = s1 * s2
+    s = 1.0 / np.sqrt(s) if abs(s) > float(np.finfo(np.float32).eps) else 1.0
+    return float(np.sqrt(max(1.0 - r * s, 0.0)))
+
+
+def vis_sim(feats_src, feats_dst):
+    """mincostflow_models.py:106-113: nan_to_num(1 - Bhattacharyya distance) of every (predecessor, current) pair."""
+    out = np.array([[1 - bhattacharyya(f1, f2) for f2 in feats_dst] for f1 in feats_src], dtype=np.float64)
+    return np.nan_to_num(out.reshape(len(feats_src), len(feats_dst)))
+
+
 def feature_hist(image, boxes, bins=180, lo=0.0, hi=1.0):
     """mincostflow_models.py:30-64 (feature_model) without cv2: the crop of each box (x, y, w, h),
     cv2.calcHist over `bins` uniform bins of [lo, hi) -- idx = floor(double(v)*a + b), a = bins/(hi-lo),
@@ -368,3 +399,16 @@ def frametiles_stack(X_tiled, frame, temporal_context=2, use_motion_filtered='ex
     st = X_tiled[a:b, :, lo:lo + n]                               # [2tc+1, ntiles, nch, ts, ts]
     st = st.transpose(1, 0, 2, 3, 4)
     return np.ascontiguousarray(st.reshape(st.shape[0], -1, *st.shape[3:]))
+
+
+def stitched_frame(X, nonempty, frame, tilesize=512, use_motion_filtered='exclude'):
+    """AxonDetections.get_frame_and_truedets(t)[0] (AxonDetections.py:355-376 -> Timelapse.stitch_tiles image half,
+    Timelapse.py:173-188) restated on the dense X: the colour channels of raw frame ``frame`` with every tile that is
+    empty at ALL timepoints (dropped from X_tiled, Timelapse.py:558) zeroed.  -> float32 [ncol, H, W]."""
+    X = np.asarray(X, np.float32)
+    lo, n = MOTION_CHANNELS[use_motion_filtered]
+    keep = np.asarray(nonempty).any(-1)
+    ts = int(tilesize)
+    H, W = X.shape[2:]
+    up = np.repeat(np.repeat(keep, ts, 0), ts, 1)[:H, :W]
+    return np.where(up[None], X[frame, lo:lo + n], np.float32(0)).astype(np.float32)

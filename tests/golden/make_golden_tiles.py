@@ -66,19 +66,30 @@ def run_reference(X, ts, tc, mode):
     ntiles = tl.X_tiled.shape[1]
     tile_yx = np.array([tl.flat_tile_idx2yx_tile_idx(i) for i in range(ntiles)], np.int32).reshape(-1, 2)
     stacks = [tl.get_frametiles_stack(t)[0].numpy() for t in range(tl.sizet)]
-    return tl.tile_info[..., 0].numpy().astype(bool), tuple(tl.X_tiled.shape), tile_yx, stacks
+    # the frame AxonDetections.get_frame_and_truedets hands to the tracker: tiles -> Timelapse.stitch_tiles
+    # (Timelapse.py:166-197; AxonDetections.py:370-372).  _get_channelsizes has no 'temp_context' branch.
+    frames = None
+    if mode != 'temp_context':
+        empty = [pd.DataFrame({'conf': [], 'anchor_x': [], 'anchor_y': []}) for _ in range(ntiles)]
+        frames = [tl.stitch_tiles(empty, torch.from_numpy(st))[1].numpy() for st in stacks]
+    return tl.tile_info[..., 0].numpy().astype(bool), tuple(tl.X_tiled.shape), tile_yx, stacks, frames
 
 
 def main():
     for seed, T, H, W, ts, tc, mode in CASES:
         X = make_X(seed, T, H, W, ts)
-        nonempty, xt_shape, tile_yx, stacks = run_reference(X, ts, tc, mode)
+        nonempty, xt_shape, tile_yx, stacks, frames = run_reference(X, ts, tc, mode)
         st = np.stack(stacks)
+        extra = {}
+        if frames is not None:
+            fr = np.stack(frames)
+            extra = dict(frame_shape=np.array(fr.shape), frame_crc=np.array([zlib.crc32(np.ascontiguousarray(f).tobytes()) for f in frames], np.uint32),
+                         frame_sample=fr.reshape(-1)[::89].copy())
         np.savez_compressed(os.path.join(HERE, f'tiles_s{seed}.npz'), seed=seed, T=T, H=H, W=W, tilesize=ts,
                             temporal_context=tc, mode=mode, nonempty=nonempty, x_tiled_shape=np.array(xt_shape),
                             tile_yx=tile_yx, stack_shape=np.array(st.shape),
                             stack_crc=np.array([zlib.crc32(s.tobytes()) for s in stacks], np.uint32),
-                            stack_sample=st.reshape(-1)[::97].copy())
+                            stack_sample=st.reshape(-1)[::97].copy(), **extra)
         print(seed, mode, 'tiles', tile_yx.shape[0], 'of', nonempty.shape[:2], 'stack', st.shape)
 
 

@@ -43,6 +43,45 @@ def test_oracle_matches_reference_fixtures(golden_dir):
         _check_against_fixture(g, nonempty, tile_yx, stacks)
 
 
+def _check_frames(g, frames):
+    if 'frame_crc' not in g.files:
+        return 0
+    frames = np.asarray(frames)
+    assert tuple(frames.shape) == tuple(g['frame_shape'])
+    assert np.array_equal(np.array([zlib.crc32(np.ascontiguousarray(f).tobytes()) for f in frames], np.uint32), g['frame_crc'])
+    assert np.array_equal(frames.reshape(-1)[::89], g['frame_sample'])
+    return len(frames)
+
+
+def test_oracle_stitched_frame_matches_reference_fixtures(golden_dir):
+    """get_frame_and_truedets(t)[0] = tiles -> Timelapse.stitch_tiles in the reference; = the dense frame with the
+    dropped tiles zeroed (oracle.stitched_frame)."""
+    n = 0
+    for g in _fixtures(golden_dir):
+        X = _make_X(golden_dir, g)
+        tc, mode, ts = int(g['temporal_context']), str(g['mode']), int(g['tilesize'])
+        if mode == 'temp_context':
+            continue
+        _, nonempty, _ = oracle.tile_frames(X, ts)
+        n += _check_frames(g, [oracle.stitched_frame(X, nonempty, t, ts, mode) for t in range(tc, X.shape[0] - tc)])
+    assert n >= 10
+
+
+@pytest.mark.gpu
+def test_cuda_stitched_frame_matches_reference_fixtures(golden_dir):
+    import torch
+    from axtrack_b200.tiling import FrameTiler
+    n = 0
+    for g in _fixtures(golden_dir):
+        X = _make_X(golden_dir, g)
+        tc, mode, ts = int(g['temporal_context']), str(g['mode']), int(g['tilesize'])
+        if mode == 'temp_context':
+            continue
+        tiler = FrameTiler(torch.from_numpy(X).cuda(), ts, tc, mode)
+        n += _check_frames(g, [tiler.stitched_frame(t).cpu().numpy() for t in range(len(tiler))])
+    assert n >= 10
+
+
 def test_oracle_context_outside_timelapse():
     X = np.ones((3, 3, 8, 8), np.float32)
     X_tiled, _, _ = oracle.tile_frames(X, 4)
