@@ -133,7 +133,10 @@ __global__ void __launch_bounds__(kK7Src * kK7Dst) k7_vis_sim_kernel(const float
     for (int k = body; k < bins; ++k) r = __dadd_rn(r, __dsqrt_rn(__dmul_rn((double)h1[k], (double)h2[k])));
     double s = __dmul_rn(lane_sum(h1, bins), lane_sum(h2, bins));
     s = fabs(s) > (double)FLT_EPSILON ? __ddiv_rn(1.0, __dsqrt_rn(s)) : 1.0;
-    const double d = __dsqrt_rn(fmax(__dadd_rn(1.0, -__dmul_rn(r, s)), 0.0));
+    // std::max(1. - result * s1, 0.) keeps a NaN (a slightly negative normalised bin makes sqrt(h1 * h2) NaN in cv2 too);
+    // fmax() would drop it
+    const double x = __dadd_rn(1.0, -__dmul_rn(r, s));
+    const double d = __dsqrt_rn(x < 0.0 ? 0.0 : x);
     double v = __dadd_rn(1.0, -d);
     if (v != v) v = 0.0;                                              // np.nan_to_num
     else if (isinf(v)) v = v > 0 ? DBL_MAX : -DBL_MAX;

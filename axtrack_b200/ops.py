@@ -294,8 +294,8 @@ def vis_sim(feats_src, feats_dst, path_len=None, max_px=500):
 
     feats_* float32 CUDA [n, bins] (or [n, bins, 1] as feature_model returns them); path_len optional int32 CUDA
     [n_src, n_dst]: entries equal to max_px are skipped (their cost is inf anyway).  -> float64 CUDA [n_src, n_dst]."""
-    fs = _need_cuda(feats_src.reshape(feats_src.shape[0], -1), 'feats_src', torch.float32)
-    fd = _need_cuda(feats_dst.reshape(feats_dst.shape[0], -1), 'feats_dst', torch.float32)
+    fs = _need_cuda(feats_src.flatten(1) if feats_src.dim() > 2 else feats_src, 'feats_src', torch.float32)
+    fd = _need_cuda(feats_dst.flatten(1) if feats_dst.dim() > 2 else feats_dst, 'feats_dst', torch.float32)
     assert fs.shape[1] == fd.shape[1]
     ns, nd, bins = fs.shape[0], fd.shape[0], fs.shape[1]
     dev = fs.device

@@ -330,10 +330,13 @@ def bhattacharyya(h1, h2):
         for k in range(body, n):
             t += float(v[k])
         return t
-    r, s1, s2 = lanes(np.sqrt(a * b)), lanes(a), lanes(b)
+    with np.errstate(invalid='ignore'):
+        r, s1, s2 = lanes(np.sqrt(a * b)), lanes(a), lanes(b)     # a normalised bin can be -1e-8: sqrt -> NaN, as in cv2
     s = s1 * s2
     s = 1.0 / np.sqrt(s) if abs(s) > float(np.finfo(np.float32).eps) else 1.0
-    return float(np.sqrt(max(1.0 - r * s, 0.0)))
+    x = 1.0 - r * s
+    with np.errstate(invalid='ignore'):
+        return float(np.sqrt(0.0 if x < 0.0 else x))          # std::max(x, 0.): a NaN stays a NaN (-> nan_to_num: 0)
 
 
 def vis_sim(feats_src, feats_dst):
