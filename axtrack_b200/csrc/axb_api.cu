@@ -477,7 +477,7 @@ int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
     const int ncell = (int)ncell_ll;
     int npad = 1;
     while (npad < ncell) npad <<= 1;
-    const size_t per_frame = axb::k1_scratch_per_frame(ncell, npad);
+    const size_t per_frame = axb::k1_scratch_per_frame(ncell, npad, ntiles);
     int rc = grow(c, &c->k1_scratch, &c->k1_scratch_bytes, per_frame * (size_t)F);
     if (rc != AXB_OK) return rc;
     axb::K1Params p;
@@ -486,6 +486,8 @@ int axb_decode_nms(axb_ctx* c, const float* Y_dev, const int32_t* tile_yx_dev,
     p.pre_conf = pre_conf_dev; p.pre_yx = pre_yx_dev; p.pre_cell = pre_cell_dev; p.n_pre = n_pre_dev;
     p.conf = conf_dev; p.yx = yx_dev; p.keep_idx = keep_idx_dev; p.n_out = n_out_dev;
     p.scratch = c->k1_scratch; p.scratch_per_frame = per_frame; p.npad = npad; p.err_flags = c->status_dev + 1;
+    if (!c->counters) AXB_CUDA(c, cudaMalloc((void**)&c->counters, 256));
+    p.wide_ctl = c->counters + 32; p.num_sms = c->num_sms;       // counters[0..7] belong to K2, [32..39] to the wide K1
     axb::launch_k1(p, (cudaStream_t)stream);
     c->launches += 1;
     AXB_CUDA(c, cudaGetLastError());

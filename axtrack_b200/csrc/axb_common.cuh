@@ -174,8 +174,11 @@ struct K1Params {
     size_t scratch_per_frame;
     int npad;                    // power of two >= ncell (sort / hash size)
     unsigned long long* err_flags;  // atomicOr: bit 2 = capacity
+    int* wide_ctl;                  // wide kernel: 8 ints of grid-wide control (zeroed by the launcher)
+    int num_sms;
 };
-size_t k1_scratch_per_frame(int ncell, int npad);
+size_t k1_scratch_per_frame(int ncell, int npad, int ntiles);
 void launch_k1(const K1Params& p, cudaStream_t stream);
+bool launch_k1_wide(const K1Params& p, cudaStream_t stream);      // false: not applicable, use the one-CTA-per-frame kernel
 
 }  // namespace axb

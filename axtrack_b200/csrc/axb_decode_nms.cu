@@ -17,70 +17,10 @@
 //      in range, kept once every better candidate in range is decided; identical to the
 //      sequential greedy result, needs only a few rounds on real data;
 //   e. compact the survivors in rank order.
-#include "axb_common.cuh"
+#include "axb_decode.cuh"
 
 namespace axb {
 
-namespace {
-
-constexpr int kK1Threads = 256;
-constexpr int kSortSmem = 4096;     // keys sorted in shared memory up to this many
-
-__device__ __forceinline__ uint32_t ordered_bits(float f) {
-    const uint32_t u = __float_as_uint(f);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-
-struct K1Work {
-    float* c_conf; int32_t* c_x; int32_t* c_y; int32_t* c_g;      // compaction order
-    float* p_conf; int32_t* p_x; int32_t* p_y; int32_t* p_tile;   // pre-NMS order
-    unsigned long long* key;                                       // [npad]
-    int32_t* s_x; int32_t* s_y; int32_t* s_p;                      // rank order
-    int32_t* head;                                                 // [2*npad]
-    int32_t* next;
-    int32_t* state;
-};
-
-__device__ __forceinline__ K1Work carve(uint8_t* base, int ncell, int npad) {
-    K1Work w;
-    size_t o = 0;
-    auto take = [&](size_t bytes) { uint8_t* p = base + o; o += (bytes + 15) & ~(size_t)15; return p; };
-    w.key = (unsigned long long*)take((size_t)npad * 8);
-    w.c_conf = (float*)take((size_t)ncell * 4);  w.c_x = (int32_t*)take((size_t)ncell * 4);
-    w.c_y = (int32_t*)take((size_t)ncell * 4);   w.c_g = (int32_t*)take((size_t)ncell * 4);
-    w.p_conf = (float*)take((size_t)ncell * 4);  w.p_x = (int32_t*)take((size_t)ncell * 4);
-    w.p_y = (int32_t*)take((size_t)ncell * 4);   w.p_tile = (int32_t*)take((size_t)ncell * 4);
-    w.s_x = (int32_t*)take((size_t)ncell * 4);   w.s_y = (int32_t*)take((size_t)ncell * 4);
-    w.s_p = (int32_t*)take((size_t)ncell * 4);
-    w.head = (int32_t*)take((size_t)npad * 2 * 4);
-    w.next = (int32_t*)take((size_t)ncell * 4);
-    w.state = (int32_t*)take((size_t)ncell * 4);
-    return w;
-}
-
-// order-preserving block compaction step: returns this thread's output slot (or -1) and
-// advances *s_base.  3 barriers.  s_wc must hold NT/32 ints.
-template <int NT>
-__device__ __forceinline__ int block_compact_slot(bool pred, int* s_base, int* s_wc) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, pred);
-    if (lane == 0) s_wc[warp] = __popc(bal);
-    __syncthreads();
-    int off = *s_base, tot = 0;
-    #pragma unroll
-    for (int w = 0; w < NT / 32; ++w) { const int c = s_wc[w]; if (w < warp) off += c; tot += c; }
-    const int slot = pred ? off + __popc(bal & ((1u << lane) - 1)) : -1;
-    __syncthreads();
-    if (threadIdx.x == 0) *s_base += tot;
-    __syncthreads();
-    return slot;
-}
-
-__device__ __forceinline__ uint32_t bin_hash(int bx, int by, uint32_t mask) {
-    return (((uint32_t)bx * 73856093u) ^ ((uint32_t)by * 19349663u)) & mask;
-}
-
-}  // namespace
 
 template <int NT>
 __global__ void __launch_bounds__(NT) k1_decode_nms_kernel(const K1Params p) {
@@ -91,7 +31,7 @@ __global__ void __launch_bounds__(NT) k1_decode_nms_kernel(const K1Params p) {
     const int f = blockIdx.x;
     const int cpt = p.Sx * p.Sy;
     const int ncell = p.ntiles * cpt;
-    const K1Work w = carve(p.scratch + (size_t)f * p.scratch_per_frame, ncell, p.npad);
+    const K1Work w = carve(p.scratch + (size_t)f * p.scratch_per_frame, ncell, p.npad, p.ntiles);
     const float* __restrict__ Y = p.Y + (size_t)f * ncell * 3;
     const float ts = (float)p.tilesize, fSx = (float)p.Sx, fSy = (float)p.Sy;
 
@@ -242,12 +182,15 @@ __global__ void __launch_bounds__(NT) k1_decode_nms_kernel(const K1Params p) {
     if (tid == 0) p.n_out[f] = s_base;
 }
 
-size_t k1_scratch_per_frame(int ncell, int npad) {
+size_t k1_scratch_per_frame(int ncell, int npad, int ntiles) {
     auto al = [](size_t b) { return (b + 15) & ~(size_t)15; };
-    return al((size_t)npad * 8) + 13 * al((size_t)ncell * 4) + al((size_t)npad * 2 * 4) + 256;
+    return al((size_t)npad * 8) + 14 * al((size_t)ncell * 4) + al((size_t)npad * 2 * 4) + al((size_t)ntiles * 4) + al((size_t)kK1MaxSlices * 4) + 256;
 }
 
 void launch_k1(const K1Params& p, cudaStream_t stream) {
+    // few frames per launch (configs[4] sweeps 1 .. 8): one CTA per frame leaves the GPU empty; a frame is spread over
+    // many CTAs of a cooperative launch instead (axb_decode_wide.cu)
+    if (launch_k1_wide(p, stream)) return;
     // one CTA per frame; frames with many grid cells (configs[4]: 36864) get 32 warps for the
     // decode pass, the bitonic sort and the NMS rounds
     if ((long long)p.ntiles * p.Sx * p.Sy > 4096) k1_decode_nms_kernel<1024><<<p.F, 1024, 0, stream>>>(p);

@@ -466,6 +466,51 @@ def test_wide_radius(cuda):
 
 
 @pytest.mark.gpu
+def test_decode_nms_wide_kernel_equals_one_cta_per_frame(cuda):
+    """Few frames per launch run on the cooperative wide kernel (a frame spread over many CTAs), many frames on one CTA
+    per frame: every output identical, also with conf ties inside a tile and across tiles, an over-full frame
+    (AXB_ERR_CAPACITY) and an empty frame."""
+    import os
+    from axtrack_b200 import ops, _lib
+    rng = np.random.default_rng(4)
+    H, W = 3072, 2048
+    tt = synth.tile_table(H, W)
+    frames = []
+    for k, n in enumerate((1500, 0, 400, 3000)):
+        dets = np.stack([rng.integers(0, H, n), rng.integers(0, W, n)], 1)
+        Y = synth.make_head_tensor(dets, H, W, seed=k)[0]
+        if k == 2:
+            Y[..., 0] = np.round(Y[..., 0], 1)                    # many exact conf ties
+        frames.append(Y)
+    Yd = cuda.from_numpy(np.stack(frames)).cuda()
+    td = cuda.from_numpy(tt).cuda()
+    outs = []
+    for env in (None, '1'):
+        if env is None:
+            os.environ.pop('AXB_K1_NO_WIDE', None)
+        else:
+            os.environ['AXB_K1_NO_WIDE'] = env
+        o = ops.decode_nms(Yd, td)
+        ops.raise_status()
+        outs.append({k: v.cpu().numpy() for k, v in o.items()})
+        small = ops.decode_nms(Yd, td, cap=500, want_pre=False)    # frames 0 and 3 hold more candidates than cap
+        with pytest.raises(_lib.AxbError):
+            ops.raise_status()
+        assert small['n_out'].cpu().numpy().tolist()[1] == 0 and small['n_out'].cpu().numpy()[0] == 0
+    os.environ.pop('AXB_K1_NO_WIDE', None)
+    a, b = outs
+    assert np.array_equal(a['n_pre'], b['n_pre']) and np.array_equal(a['n_out'], b['n_out']) and a['n_out'][1] == 0
+    for f in range(4):
+        npre, nout = int(a['n_pre'][f]), int(a['n_out'][f])
+        for k in ('pre_conf', 'pre_yx', 'pre_cell'):
+            assert np.array_equal(a[k][f, :npre], b[k][f, :npre]), (f, k)
+        for k in ('conf', 'yx', 'keep_idx'):
+            assert np.array_equal(a[k][f, :nout], b[k][f, :nout]), (f, k)
+        want = oracle.decode_stitch_nms(frames[f], tt)
+        assert np.array_equal(a['keep_idx'][f, :nout], want['keep_idx']), f
+
+
+@pytest.mark.gpu
 def test_decode_nms_8192_frames(cuda):
     """BASELINE configs[4] shape: 8192x8192 frames = 256 tiles x 12x12 cells, thousands of candidates
     per frame (the sort leaves shared memory), several frames per launch; survivor indices,

@@ -106,7 +106,8 @@ def test_cuda_matches_reference_fixtures_and_oracle(golden_dir):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('H,W,ts', [(1000, 1030, 512), (1024, 1024, 512), (130, 67, 50), (37, 41, 512), (600, 520, 512), (200, 24, 128)])
+@pytest.mark.parametrize('H,W,ts', [(1000, 1030, 512), (1024, 1024, 512), (130, 67, 50), (37, 41, 512), (600, 520, 512), (200, 24, 128),
+                                    (1000, 1028, 256), (300, 516, 128), (1536, 2048, 512)])
 def test_cuda_matches_oracle_ragged(H, W, ts):
     """Vector path (W % 4 == 0) and scalar path, images smaller than a tile, ragged borders, NaN pixels."""
     import torch
