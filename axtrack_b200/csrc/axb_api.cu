@@ -27,7 +27,6 @@ struct axb_ctx {
 
     // K2
     uint32_t* k2_fast_scratch = nullptr;   int k2_fast_ctas = 0;
-    uint32_t* k2_pool_scratch = nullptr;   int k2_pool_ctas = 0;
     uint32_t* k2_gen_scratch = nullptr;    int k2_gen_ctas = 0;
     uint32_t* k2_wide_scratch = nullptr;   // max_px > 511: per general CTA kGenScratchWordsWide (allocated on first use)
     uint8_t* trace_par_wide = nullptr;
@@ -95,10 +94,6 @@ int ensure_k2(axb_ctx* c, int n_pairs, int total_src) {
         c->k2_fast_ctas = c->num_sms * std::max(axb::kFastCtasPerSm, axb::kSparseCtasPerSm);
         AXB_CUDA(c, cudaMalloc((void**)&c->k2_fast_scratch, (size_t)c->k2_fast_ctas * axb::kFastScratchWords * sizeof(uint32_t)));
     }
-    if (!c->k2_pool_scratch) {
-        c->k2_pool_ctas = c->num_sms * axb::kPoolCtasPerSm;
-        AXB_CUDA(c, cudaMalloc((void**)&c->k2_pool_scratch, (size_t)c->k2_pool_ctas * axb::kPoolScratchWords * sizeof(uint32_t)));
-    }
     if (!c->k2_gen_scratch) {
         c->k2_gen_ctas = c->num_sms;
         AXB_CUDA(c, cudaMalloc((void**)&c->k2_gen_scratch, (size_t)c->k2_gen_ctas * axb::kGenScratchWords * sizeof(uint32_t)));
@@ -152,7 +147,7 @@ void axb_destroy(axb_ctx* c) {
     if (c->ev_in) cudaEventDestroy(c->ev_in);
     for (int i = 0; i < 2; ++i) if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
-    cudaFree(c->k2_fast_scratch); cudaFree(c->k2_pool_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
+    cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
     cudaFree(c->trace_par); cudaFree(c->trace_iota); cudaFree(c->k2_wide_scratch); cudaFree(c->trace_par_wide);
     cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
@@ -247,7 +242,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     const bool wide = max_px > axb::kFastMaxPx;
     if (wide && !c->k2_wide_scratch)
         AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kWideCtasPerSm * axb::kGenScratchWordsWide * sizeof(uint32_t)));
-    if (!wide) axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
+    axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
     int* const work_prefix = c->prefix_dev;
     int* const all_prefix = c->prefix_dev + c->prefix_cap;
     int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
@@ -261,25 +256,25 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
     p.max_px = max_px; p.hash_smem = 0; p.sparse_words = axb::kSparseWords; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = wide ? c->k2_wide_scratch : c->k2_gen_scratch;
-    p.pool_scratch = c->k2_pool_scratch;
     p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
     p.orig_base = orig_base;
-    if (wide) {      // beyond the tile-word kernels' window: every source goes through the wide all-levels kernel
-        axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
+    if (wide) {
+        // max_px 512 .. 1023: sparse tile-word windows on the 256-column circle first (level 0, 2 CTAs per SM); what they
+        // cannot hold or answer goes to the all-levels kernel with its bitmaps in global memory.  AXB_K2_WIDE_GENERAL_ONLY
+        // (round-1 behaviour, for A/B timing): every source on the all-levels kernel.
+        static const bool general_only = getenv("AXB_K2_WIDE_GENERAL_ONLY") != nullptr;
+        if (general_only) axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
+        else axb::launch_k2_sparse_wide(p, std::max(1, std::min(c->num_sms * axb::kWideSparseCtasPerSm, total_src)), s);
         axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * axb::kWideCtasPerSm, total_src)), s);
-        c->launches += 3;
+        c->launches += 4;
         AXB_CUDA(c, cudaGetLastError());
         return AXB_OK;
     }
-    // AXB_K2_FORCE_POOL: the pooled experiment (kPoolSlots searches per CTA share one wavefront loop, axb_search_pool.cu).
-    // Measured on B200 (profiles/r02a_*): bit-identical results, 13.6 ms against 12.0 ms for one search per CTA on the
-    // config-2 block -- 7 % fewer instructions but half the warps -- so one search per CTA stays the shipped path.
-    static const bool force_pool = getenv("AXB_K2_FORCE_POOL") != nullptr;
-    if (force_pool)
-        axb::launch_k2_pool(p, std::max(1, std::min(c->k2_pool_ctas, (total_src + axb::kPoolSlots - 1) / axb::kPoolSlots)), s);
-    else
-        axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
+    // one search per CTA.  Measured alternatives (profiles/r02a_*, bit-identical results): one WARP per search 13.3 ms and
+    // two searches POOLED per CTA 13.6 ms against 12.0 ms on the config-2 block -- fewer instructions, but too few warps
+    // per SM to hide the ~6 cycles between dependent instructions; both were removed again (git history has them).
+    axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
     axb::launch_k2_fast(p, std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src)), s);
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
     c->launches += 5;

@@ -43,18 +43,10 @@ constexpr int kSparseQCap = 144;
 constexpr int kSparseHash = 512;
 constexpr int kSparseHashMaxLoad = 320;
 constexpr int kSparseCtasPerSm = 10;
-// pooled level-0 kernel (k2_pool_kernel): kPoolSlots searches per CTA share one wavefront loop
-#ifndef AXB_POOL_SLOTS
-#define AXB_POOL_SLOTS 2
-#endif
-#ifndef AXB_POOL_WARPS
-#define AXB_POOL_WARPS 3
-#endif
-constexpr int kPoolSlots = AXB_POOL_SLOTS;
-constexpr int kPoolWarps = AXB_POOL_WARPS;
-constexpr int kPoolCtasPerSm = kSparseCtasPerSm / kPoolSlots;
-constexpr int kPoolWords = kSparseWords;          // non-zero tile words per slot
-constexpr int kPoolQCap = 48 * kPoolSlots * 3 / kPoolWarps * kPoolWarps;   // shared-memory frontier entries per buffer (all warp segments)
+// sparse window on the 256-column circle (max_px 512 .. 1023): 2 CTAs per SM
+constexpr int kWideWords = 20480;     // non-zero tile words a wide sparse window can hold (80 KB; the whole diamond: 65 792)
+constexpr int kWideQCap = 384;
+constexpr int kWideSparseCtasPerSm = 2;
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
@@ -79,7 +71,6 @@ struct K2Params {
     int32_t* path_len;
     uint8_t* unreachable;
     float* wcost;
-    uint32_t* pool_scratch;      // per pooled CTA: kPoolScratchWords
     uint32_t* fast_scratch;      // per fast CTA: kCandCap + 2*kFastGQCap words
     uint32_t* gen_scratch;       // per general CTA: kCandCap + 4*kGCap words
     int* counters;               // [0] sparse ticket, [1] general list length, [2] general ticket, [3] dense list length, [4] dense ticket
@@ -100,8 +91,8 @@ inline size_t k2_fast_smem_bytes(int max_px) {      // dense window + queues + h
 inline size_t k2_sparse_smem_bytes(int max_px) {    // packed words + (presence, base) per 32 tile columns + queues + hash
     return ((size_t)kSparseWords + (size_t)k2_tile_rows(max_px) * 8 + 4 * kSparseQCap) * sizeof(uint32_t);   // the target hash lives in the CTA's global scratch
 }
-inline size_t k2_pool_smem_bytes(int max_px) {      // kPoolSlots x (packed words + presence table) + two frontier buffers (+ seed segment)
-    return ((size_t)kPoolSlots * ((size_t)kPoolWords + (size_t)k2_tile_rows(max_px) * 8) + 4 * (size_t)(kPoolQCap + 2 * kPoolSlots)) * sizeof(uint32_t);
+inline size_t k2_sparse_wide_smem_bytes(int max_px) {   // packed words + (presence, base) per 32 of 256 tile columns + queues
+    return ((size_t)kWideWords + (size_t)k2_tile_rows(max_px) * 16 + 4 * kWideQCap) * sizeof(uint32_t);
 }
 inline size_t k2_gen_smem_bytes(int max_px) {
     return (2 * (size_t)(max_px + 1) * kRowWords + 2 * kGenQCap + kHashSize + 2 * kSeedCal) * sizeof(uint32_t);
@@ -110,8 +101,6 @@ inline size_t k2_gen_wide_smem_bytes() {            // bitmaps in global scratch
     return (2 * (size_t)kGenQCap + kHashSize + 2 * kSeedCalWide) * sizeof(uint32_t);
 }
 constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap + kSparseHash;
-// per pooled CTA: frontier overflow [2][kFastGQCap] (8 B) | per slot candidates + target hash | pending hits per warp (16 B)
-constexpr size_t kPoolScratchWords = 4 * (size_t)kFastGQCap + (size_t)kPoolSlots * (kCandCap + kSparseHash) + (size_t)kPoolWarps * 64 * 4;
 constexpr size_t kTraceParBytes = (size_t)(kFastMaxPx + 1) * kRowBits;
 constexpr size_t kTraceParBytesWide = (size_t)(AXB_MAX_PX + 1) * 2 * kRowBits;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;
@@ -135,7 +124,7 @@ void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, i
 void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
-void launch_k2_pool(const K2Params& p, int grid, cudaStream_t stream);
+void launch_k2_sparse_wide(const K2Params& p, int grid, cudaStream_t stream);   // max_px 512 .. 1023
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);     // max_px > kFastMaxPx: the wide kernel
 void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);

@@ -81,9 +81,11 @@ enum ItemResult { kItemDone = 0, kItemToGeneral = 1, kItemToDense = 2 };
 // One work item = one source of a chain leader, processed by the whole CTA.  All control flow is
 // CTA-uniform.  kItemToGeneral: level 0 cannot answer; kItemToDense (sparse only): the window has
 // more non-zero tile words than the sparse layout holds.
-template <bool SPARSE>
+template <bool SPARSE, int LOGC = 7>
 __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
-    using C = Cfg<SPARSE>;
+    using C = Cfg<SPARSE, LOGC>;
+    using G = TW<LOGC>;
+    static_assert(SPARSE || LOGC == 7, "the dense window exists for the 128-column circle only");
     constexpr int NT = kFastThreads;
     constexpr int HASH = C::kHash;
     const int tid = threadIdx.x;
@@ -94,8 +96,8 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
 
     // shared memory: window words | (sparse) presence/base table | two frontier buffers | target hash
     uint32_t* const WIN = smem;
-    uint2* const PB = (uint2*)(WIN + (SPARSE ? p.sparse_words : NR * kTC));
-    uint2* const q0 = PB + (SPARSE ? NR * 4 : 0);          // [2][kNW][kSeg] (bits, key)
+    uint2* const PB = (uint2*)(WIN + (SPARSE ? p.sparse_words : NR * G::TC));
+    uint2* const q0 = PB + (SPARSE ? NR * G::GROUPS : 0);  // [2][kNW][kSeg] (bits, key)
     // target hash: probed only for the few words flagged as holding a target, so the sparse
     // kernel keeps it in the CTA's global scratch (L2) and spends the shared memory on residency
     // (unless the launch is too small to fill the SMs: then latency counts, p.hash_smem)
@@ -185,9 +187,9 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     AXB_ASSERT(slot < (uint32_t)kCandCap && slot < 2048u);
                     cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
                     int bit;
-                    const uint32_t key = cell_key(dy, dx, w.oy, w.ox, NR, bit);
-                    AXB_ASSERT(((key & 0x7FFFu) >> 7) < (uint32_t)NR && bit >= 0 && bit < 32);
-                    const uint32_t entry = (key << 16) | ((uint32_t)bit << 11) | slot;
+                    const uint32_t key = cell_key<LOGC>(dy, dx, w.oy, w.ox, NR, bit);
+                    AXB_ASSERT(((key & G::WMASK) >> LOGC) < (uint32_t)NR && bit >= 0 && bit < 32 && slot < (1u << G::SLOTB));
+                    const uint32_t entry = (key << G::ESH) | ((uint32_t)bit << G::SLOTB) | slot;
                     uint32_t h = hash_slot<HASH>(key);
                     while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (HASH - 1);
                 }
@@ -197,7 +199,8 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
         const int ncand = ctl.ncand;
         if (ncand > 0) {
             AXB_T(0, tclk);
-            stage_window<SPARSE>(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, kNW);
+            if (LOGC == 7) stage_window<SPARSE>(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, kNW);
+            else stage_window_wide(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, kNW);
             __syncthreads();
             AXB_T(1, tclk);
             if (SPARSE && ctl.alloc > p.sparse_words) return kItemToDense;
@@ -205,22 +208,22 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 for (int i = tid; i < HASH; i += NT) {
                     const uint32_t e = hash[i];
                     if (e != kEmpty) {
-                        const uint32_t key = e >> 16;
-                        atomicOr(&PB[(key & 0x7FFFu) >> 5].y, 1u << (16u + ((key & 31u) >> 1)));
+                        const uint32_t key = e >> G::ESH;
+                        atomicOr(&PB[(key & G::WMASK) >> 5].y, 1u << (16u + ((key & 31u) >> 1)));
                     }
                 }
             }
             if (tid == 0) {            // close the source cell, seed the search with it
                 int bit;
-                const uint32_t key = cell_key(0, 0, w.oy, w.ox, NR, bit);
-                int widx = (int)(key & 0x7FFFu);
+                const uint32_t key = cell_key<LOGC>(0, 0, w.oy, w.ox, NR, bit);
+                int widx = (int)(key & G::WMASK);
                 bool there = true;
                 if (SPARSE) {
                     const uint2 pb = PB[widx >> 5];
                     there = (pb.x >> (widx & 31)) & 1u;
                     widx = (int)(pb.y & 0xFFFFu) + __popc(pb.x & ((1u << (widx & 31)) - 1u));
                 }
-                AXB_ASSERT(!there || widx < (SPARSE ? p.sparse_words : NR * kTC));
+                AXB_ASSERT(!there || widx < (SPARSE ? p.sparse_words : NR * G::TC));
                 if (there) WIN[widx] &= ~(1u << bit);
                 q0[0] = make_uint2(1u << bit, key);
                 ctl.wc[0][0] = 1; ctl.wc[0][1] = 0; ctl.wc[0][2] = 0; ctl.wc[0][3] = 0;
@@ -238,9 +241,9 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             // sparse window holds no such word
             // (sparse: PB[].y = index of the group's first word | target flags << 16, returned in aux)
             auto resolve = [&](uint32_t key, uint32_t& want, uint32_t& aux) -> uint32_t {
-                const uint32_t widx = key & 0x7FFFu;
+                const uint32_t widx = key & G::WMASK;
                 if (!SPARSE) return win_s + 4u * widx;
-                AXB_ASSERT(!want || (widx >> 7) < (uint32_t)NR);
+                AXB_ASSERT(!want || (widx >> LOGC) < (uint32_t)NR);
                 const uint2 pb = lds64_if(pb_s + 8u * (widx >> 5), want);
                 const uint32_t bit = 1u << (widx & 31u);
                 if (!(pb.x & bit)) want = 0u;
@@ -283,14 +286,15 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     uint32_t cd1 = (f & 0x80808080u) >> 7;
                     uint32_t cd2 = (f & 0x01010101u) << 7;
                     uint32_t cd3 = f >> 24, cd4 = f << 24;
-                    const uint32_t rowk = k0 & ~127u;
-                    const uint32_t k1 = rowk | ((k0 + 1u) & 127u);
-                    const uint32_t k2 = rowk | ((k0 - 1u) & 127u);
-                    uint32_t k3 = k0 + 128u, k4 = k0 - 128u;
-                    const uint32_t hr = k0 >> 7;                      // half << 8 | folded row
-                    if (hr == lastU) k3 = 0x8000u | ((k0 + 64u) & 127u);              // tile row 0 -> 1
-                    if (hr == 256u) k4 = (lastU << 7) | ((k0 + 64u) & 127u);         // tile row 1 -> 0
-                    if (hr == 255u + lastU) cd3 = 0u;                 // window borders (never open anyway)
+                    constexpr uint32_t CM = (uint32_t)G::TC - 1u;
+                    const uint32_t rowk = k0 & ~CM;
+                    const uint32_t k1 = rowk | ((k0 + 1u) & CM);
+                    const uint32_t k2 = rowk | ((k0 - 1u) & CM);
+                    uint32_t k3 = k0 + (uint32_t)G::TC, k4 = k0 - (uint32_t)G::TC;
+                    const uint32_t hr = k0 >> LOGC;                   // half << FRB | folded row
+                    if (hr == lastU) k3 = G::HALFBIT | ((k0 + (uint32_t)G::HALF) & CM);           // tile row 0 -> 1
+                    if (hr == (1u << G::FRB)) k4 = (lastU << LOGC) | ((k0 + (uint32_t)G::HALF) & CM);   // tile row 1 -> 0
+                    if (hr == (1u << G::FRB) - 1u + lastU) cd3 = 0u;  // window borders (never open anyway)
                     if (hr == 0u) cd4 = 0u;
                     uint32_t aux0 = 0u, auxn = 0u;
                     const uint32_t a0 = resolve(k0, cd0, aux0), a1 = resolve(k1, cd1, auxn), a2 = resolve(k2, cd2, auxn);
@@ -313,7 +317,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     // targets among the cells being expanded (hop j, path length j + 1)
                     if (__any_sync(kFull, maybe)) {
                         int ns = 0;
-                        if (maybe) ns = probe_settle<HASH>(p, hash, cand, ch, k0, f, j);
+                        if (maybe) ns = probe_settle<HASH, LOGC>(p, hash, cand, ch, k0, f, j);
                         ws += __reduce_add_sync(kFull, ns);
                     }
                     // append the claims to this warp's segment of the next frontier, lane-major
@@ -402,6 +406,37 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
         const int r = run_item_fast<false>(p, item, smem, gscr, ctl);
         if (r == kItemToGeneral && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
     }
+}
+
+// max_px 512 .. 1023: the same sparse-window search on the 256-column circle (257 folded rows, 18-bit word keys).
+// Windows with more non-zero tile words than the layout holds, and everything level 0 cannot answer, go to the
+// all-levels kernel (k2_general_wide_kernel).
+__global__ void __launch_bounds__(kFastThreads, kWideSparseCtasPerSm) k2_sparse_wide_kernel(const K2Params p) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ Ctl ctl;
+    uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
+    const int total = p.work_prefix[p.n_pairs];
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[0], 1);
+        __syncthreads();
+        const int item = ctl.item;
+        if (item >= total) break;
+        const int r = run_item_fast<true, 8>(p, item, smem, gscr, ctl);
+        if (threadIdx.x == 0 && r != kItemDone) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+    }
+}
+
+void launch_k2_sparse_wide(const K2Params& p, int grid, cudaStream_t stream) {
+    static unsigned long long attr_set = 0ull;
+    if (first_use_on_device(attr_set)) {
+        cudaFuncSetAttribute(k2_sparse_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_sparse_wide_smem_bytes(AXB_MAX_PX));
+        cudaFuncSetAttribute(k2_sparse_wide_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    }
+    K2Params q = p;
+    q.hash_smem = 0;
+    q.sparse_words = kWideWords;
+    k2_sparse_wide_kernel<<<grid, kFastThreads, k2_sparse_wide_smem_bytes(p.max_px), stream>>>(q);
 }
 
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {

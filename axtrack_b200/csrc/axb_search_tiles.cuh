@@ -17,7 +17,23 @@ namespace axb {
 namespace {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
-constexpr int kTC = 128;                  // tile columns per folded row
+constexpr int kTC = 128;                  // tile columns per folded row (max_px <= 511)
+
+// Geometry of the folded window for a circle of 2^LOGC tile columns: LOGC = 7 (1024 px, max_px <= 511) and
+// LOGC = 8 (2048 px, max_px <= 1023; the reference honours any max_px_assoc_dist, AxonDetections.py:623-625,736).
+template <int LOGC> struct TW {
+    static constexpr int TC = 1 << LOGC;                 // tile columns of a folded row
+    static constexpr int HALF = TC / 2;                  // where the upper half's source column sits
+    static constexpr int FRB = LOGC + 1;                 // bits of a folded row index (NR <= 129 / 257)
+    static constexpr int WB = LOGC + FRB;                // bits of a window word index = folded row << LOGC | column
+    static constexpr uint32_t WMASK = (1u << WB) - 1u;
+    static constexpr uint32_t HALFBIT = 1u << WB;        // key of a tile word = half << WB | word index
+    static constexpr int KB = WB + 1;                    // key bits: 16 / 18
+    static constexpr int ESH = 32 - KB;                  // target-hash entry = key << ESH | bit << SLOTB | candidate slot
+    static constexpr int SLOTB = ESH - 5;                // 11 / 9 bits of candidate slot
+    static constexpr int GROUPS = TC / 32;               // presence-table entries per folded row
+};
+static_assert(TW<7>::HALFBIT == 0x8000u && TW<7>::ESH == 16 && TW<7>::SLOTB == 11, "the 128-column layout of round 1");
 
 __device__ __forceinline__ uint32_t lanemask_lt() {
     uint32_t m;
@@ -25,24 +41,26 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
     return m;
 }
 
+template <int LOGC = 7>
 __device__ __forceinline__ uint32_t make_key(int half, int fr, int col) {
-    return ((uint32_t)half << 15) | ((uint32_t)fr << 7) | (uint32_t)col;
+    return ((uint32_t)half << TW<LOGC>::WB) | ((uint32_t)fr << LOGC) | (uint32_t)col;
 }
 // cell (dy, dx) relative to the source -> key and bit of its tile word
+template <int LOGC = 7>
 __device__ __forceinline__ uint32_t cell_key(int dy, int dx, int oy, int ox, int NR, int& bit) {
     const int cy = dy + oy, cx = dx + ox;
     const int tr = cy >> 2;
     const int half = tr > 0;
     const int fr = half ? tr - 1 : tr + NR - 1;
-    const int col = ((cx >> 3) + (half ? 0 : 64)) & (kTC - 1);
+    const int col = ((cx >> 3) + (half ? 0 : TW<LOGC>::HALF)) & (TW<LOGC>::TC - 1);
     bit = ((cy & 3) << 3) | (cx & 7);
-    return make_key(half, fr, col);
+    return make_key<LOGC>(half, fr, col);
 }
 
 template <int HASH> __device__ __forceinline__ uint32_t hash_slot(uint32_t key);
 template <> __device__ __forceinline__ uint32_t hash_slot<1024>(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
 template <> __device__ __forceinline__ uint32_t hash_slot<512>(uint32_t key) { return (key * 0x9E3779B1u) >> 23; }
-static_assert(kCandCap <= 2048, "hash entries keep 11 bits of candidate slot");
+static_assert(kCandCap <= 2048 && kSparseHashMaxLoad <= 512, "hash entries keep 11 (wide layout: 9) bits of candidate slot");
 
 struct Chain {
     long long orow[kMaxChain];      // first output element of this source's row, per member pair
@@ -128,14 +146,17 @@ constexpr int kNW = kFastThreads / 32;            // warps per search
 constexpr int kGSeg = kFastGQCap / kNW;           // global overflow entries per warp per buffer
 static_assert(kNW >= 1 && kNW <= 4, "Ctl::wc holds one word per warp in one 16-byte row");
 
-template <bool SPARSE> struct Cfg;
-template <> struct Cfg<false> {
+template <bool SPARSE, int LOGC = 7> struct Cfg;
+template <> struct Cfg<false, 7> {
     static constexpr int kQCap = kFastQCap, kSeg = kFastQCap / kNW, kHash = kHashSize, kMaxLoad = kHashMaxLoad;
 };
-template <> struct Cfg<true> {
+template <> struct Cfg<true, 7> {
     static constexpr int kQCap = kSparseQCap, kSeg = kSparseQCap / kNW, kHash = kSparseHash, kMaxLoad = kSparseHashMaxLoad;
 };
-static_assert(kFastQCap / kNW + kGSeg < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
+template <> struct Cfg<true, 8> {      // max_px 512 .. 1023: about twice the frontier entries per wave
+    static constexpr int kQCap = kWideQCap, kSeg = kWideQCap / kNW, kHash = kSparseHash, kMaxLoad = kSparseHashMaxLoad;
+};
+static_assert(kFastQCap / kNW + kGSeg < 0x8000 && kWideQCap / kNW + kGSeg < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -169,16 +190,17 @@ __device__ __forceinline__ void sts64_if(uint32_t a, uint32_t x, uint32_t y, uin
 
 // Slow path of the target probe: the hash slot of tile word `key` is occupied.  The cells
 // `claimed` of the word were reached with j mask pixels on the path (hop j, path length j+1).
-template <int HASH>
+template <int HASH, int LOGC = 7>
 __device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash, const uint32_t* cand,
                                          const Chain& ch, uint32_t key, uint32_t claimed, int j) {
+    using G = TW<LOGC>;
     int n = 0;
     uint32_t h = hash_slot<HASH>(key);
     for (;;) {
         const uint32_t e = hash[h];
         if (e == kEmpty) break;
-        if ((e >> 16) == key && ((claimed >> ((e >> 11) & 31u)) & 1u)) {
-            const uint32_t c = cand[e & 0x7FFu];
+        if ((e >> G::ESH) == key && ((claimed >> ((e >> G::SLOTB) & 31u)) & 1u)) {
+            const uint32_t c = cand[e & ((1u << G::SLOTB) - 1u)];
             const long long o = ch.orow[c >> 30] + (long long)(c & 0x3FFFFFFFu);
             p.path_len[o] = j + 1;
             p.unreachable[o] = 0;
@@ -244,6 +266,75 @@ __device__ __noinline__ void stage_window(const Win w, uint32_t* WIN, uint2* PB,
             for (int k = 0; k < 4; ++k)
                 if (t[k] != 0u) {
                     if (idx < cap_words) WIN[idx] = t[k];
+                    ++idx;
+                }
+        }
+    }
+}
+
+
+// The same for the 256-column circle (max_px 512 .. 1023), sparse layout only: one warp per folded row, each lane
+// TWO quads of four folded tile columns (4*lane .. and 128 + 4*lane ..), eight presence groups per row.  A folded
+// column holds tile column col-128 or col+128 of the upper tile row and col or col-256 of the lower one.
+__device__ __noinline__ void stage_window_wide(const Win w, uint32_t* WIN, uint2* PB, int* alloc, const int cap_words,
+                                               const int row0, const int row_step) {
+    constexpr int TC = TW<8>::TC, HALF = TW<8>::HALF;
+    const int lane = threadIdx.x & 31;
+    for (int fr = row0; fr < w.NR; fr += row_step) {
+        const int tr_u = fr - w.NR + 1, tr_l = fr + 1;
+        int hwi_u, hwo_u, hwi_l, hwo_l;
+        row_half_widths(w, tr_u, hwi_u, hwo_u);
+        row_half_widths(w, tr_l, hwi_l, hwo_l);
+        if (tr_l > w.NR - 1) hwo_l = -64;               // no lower tile row: nothing in span
+        uint32_t t[2][4] = {{0u, 0u, 0u, 0u}, {0u, 0u, 0u, 0u}};
+        #pragma unroll
+        for (int part = 0; part < 2; ++part) {
+            const int q4 = 4 * lane + part * HALF;      // first folded column of this lane's quad
+            #pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int tr = h ? tr_l : tr_u, hwi = h ? hwi_l : hwi_u, hwo = h ? hwo_l : hwo_u;
+                int xa, xb;
+                const uint4* sa = window_quad(w, tr, h ? q4 : q4 - HALF, hwo, xa);
+                const uint4* sb = window_quad(w, tr, h ? q4 - TC : q4 + HALF, hwo, xb);
+                uint4 va = sa ? __ldg(sa) : make_uint4(0u, 0u, 0u, 0u);
+                uint4 vb = sb ? __ldg(sb) : make_uint4(0u, 0u, 0u, 0u);
+                if (sa) clip_quad(w, tr, xa, hwi, va);
+                if (sb) clip_quad(w, tr, xb, hwi, vb);
+                t[part][0] |= va.x | vb.x; t[part][1] |= va.y | vb.y; t[part][2] |= va.z | vb.z; t[part][3] |= va.w | vb.w;
+            }
+        }
+        // presence bits: group = part * 4 + lane / 8 (8 lanes x 4 columns = 32 columns)
+        const int sh = 4 * (lane & 7), grp = lane >> 3;
+        uint32_t pr[8];
+        int cnt[8];
+        #pragma unroll
+        for (int part = 0; part < 2; ++part) {
+            const uint32_t nib = (t[part][0] != 0u ? 1u : 0u) | (t[part][1] != 0u ? 2u : 0u) | (t[part][2] != 0u ? 4u : 0u) | (t[part][3] != 0u ? 8u : 0u);
+            #pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                pr[part * 4 + g] = __reduce_or_sync(kFull, grp == g ? nib << sh : 0u);
+                cnt[part * 4 + g] = __popc(pr[part * 4 + g]);
+            }
+        }
+        int total = 0;
+        #pragma unroll
+        for (int g = 0; g < 8; ++g) total += cnt[g];
+        int base = 0;
+        if (lane == 0) base = atomicAdd(alloc, total);
+        base = __shfl_sync(kFull, base, 0);
+        #pragma unroll
+        for (int part = 0; part < 2; ++part) {
+            const int mg = part * 4 + grp;
+            int gbase = base;
+            uint32_t mypr = 0u;
+            #pragma unroll
+            for (int g = 0; g < 8; ++g) { gbase += g < mg ? cnt[g] : 0; mypr = g == mg ? pr[g] : mypr; }
+            if ((lane & 7) == 0) PB[fr * 8 + mg] = make_uint2(mypr, (uint32_t)gbase);
+            int idx = gbase + __popc(mypr & ((1u << sh) - 1u));
+            #pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (t[part][k] != 0u) {
+                    if (idx < cap_words) WIN[idx] = t[part][k];
                     ++idx;
                 }
         }

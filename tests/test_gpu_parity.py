@@ -436,9 +436,11 @@ def test_window_rim_at_largest_radii(cuda):
 @pytest.mark.gpu
 def test_wide_radius(cuda):
     """max_px_assoc_dist is an attribute the reference honours at any value (AxonDetections.py:623-625,
-    736; SURVEY 8d sweeps {500, 1000}): 512 <= max_px <= 1023 runs every source on the wide
-    all-levels kernel (2048-bit folded rows, bitmaps in global scratch).  Corridor mask with sources
-    on and off it, an open field with targets on the rim, and a frame smaller than the window."""
+    736; SURVEY 8d sweeps {500, 1000}): 512 <= max_px <= 1023 runs on sparse tile-word windows folded on a
+    256-column circle (k2_sparse_wide_kernel); sources level 0 cannot answer and windows too dense for the
+    layout go to the wide all-levels kernel (2048-bit folded rows, bitmaps in global scratch).  Corridor mask
+    with sources on and off it, an open field with targets on the rim (dense: all-levels kernel), comb masks
+    with targets on the rim (sparse), and a frame smaller than the window."""
     rng = np.random.default_rng(21)
     H, W = 1500, 1700
     mask = synth.make_mask(H, W, seed=9, pitch=(90, 200), width=(6, 16))
@@ -460,6 +462,25 @@ def test_wide_radius(cuda):
         dst = np.array(dst, np.int32)
         src = np.array([[sy, sx]], np.int32)
         _check(_gpu_cost(cuda, ones, src, dst, max_px), oracle.cost_matrix_rule(ones, src, dst, max_px), ('rim', max_px))
+    # sparse wide windows at the rim of the diamond (256-column circle): comb mask, every source alignment class
+    Hc, Wc = 2100, 2200
+    for max_px in (1000, 1016, 1023):
+        for k in range(8):
+            sy, sx = 1048 + k % 4, 1090 + 5 * k
+            comb = np.zeros((Hc, Wc), np.uint8)
+            comb[sy % 24::24, :] = 1
+            comb[:, sx] = 1
+            dst = []
+            for y in np.arange(sy % 24, Hc, 24):
+                hw = max_px - abs(int(y) - sy)
+                for side in (-1, 1):
+                    for inward in range(0, 10):
+                        x = sx + side * (hw - inward)
+                        if hw - inward >= 0 and 0 <= x < Wc:
+                            dst.append((y, x))
+            src = np.array([[sy, sx]], np.int32)
+            dst = np.array(dst, np.int32)
+            _check(_gpu_cost(cuda, comb, src, dst, max_px), oracle.cost_matrix_rule(comb, src, dst, max_px), ('comb', max_px, sy, sx))
     small = (rng.random((90, 130)) < 0.7).astype(np.uint8)
     pts = np.stack([rng.integers(0, 90, 30), rng.integers(0, 130, 30)], 1).astype(np.int32)
     _check(_gpu_cost(cuda, small, pts[:10], pts, 900), oracle.cost_matrix_rule(small, pts[:10], pts, 900), 'small frame')
