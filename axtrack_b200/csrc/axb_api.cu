@@ -265,10 +265,18 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
         // (round-1 behaviour, for A/B timing): every source on the all-levels kernel.
         static const bool general_only = getenv("AXB_K2_WIDE_GENERAL_ONLY") != nullptr;
         if (general_only) axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
-        else axb::launch_k2_sparse_wide(p, std::max(1, std::min(c->num_sms * axb::kWideSparseCtasPerSm, total_src)), s);
+        else axb::launch_k2_sparse_wide(p, std::max(1, std::min(c->num_sms * axb::kWideSparseCtasPerSm, total_src)),
+                                        std::max(1, std::min(c->num_sms, total_src)), s);
         axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * axb::kWideCtasPerSm, total_src)), s);
-        c->launches += 4;
+        c->launches += 5;
         AXB_CUDA(c, cudaGetLastError());
+        static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;     // profiling aid: where the work items went
+        if (dbg) {
+            int h[8];
+            cudaStreamSynchronize(s);
+            cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[axb] wide K2: %d sources, %d to the second pass, %d to the all-levels kernel\n", total_src, h[3], h[1]);
+        }
         return AXB_OK;
     }
     // one search per CTA.  Measured alternatives (profiles/r02a_*, bit-identical results): one WARP per search 13.3 ms and

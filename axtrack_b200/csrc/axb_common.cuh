@@ -124,7 +124,7 @@ void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, i
 void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
-void launch_k2_sparse_wide(const K2Params& p, int grid, cudaStream_t stream);   // max_px 512 .. 1023
+void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t stream);   // max_px 512 .. 1023: two passes
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);     // max_px > kFastMaxPx: the wide kernel
 void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);

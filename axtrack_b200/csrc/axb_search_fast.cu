@@ -411,32 +411,47 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
 // max_px 512 .. 1023: the same sparse-window search on the 256-column circle (257 folded rows, 18-bit word keys).
 // Windows with more non-zero tile words than the layout holds, and everything level 0 cannot answer, go to the
 // all-levels kernel (k2_general_wide_kernel).
-__global__ void __launch_bounds__(kFastThreads, kWideSparseCtasPerSm) k2_sparse_wide_kernel(const K2Params p) {
+// First pass (SECOND = false): every work item, windows of up to kWideWords non-zero tile words, 2 CTAs per SM; items
+// whose window holds more go to the dense list.  Second pass (SECOND = true): those items with windows of up to
+// kWideWords2 words, 1 CTA per SM.  What neither holds (e.g. an all-ones mask: 65 792 words) goes to the all-levels kernel.
+template <bool SECOND>
+__global__ void __launch_bounds__(kFastThreads, SECOND ? 1 : kWideSparseCtasPerSm) k2_sparse_wide_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
-    const int total = p.work_prefix[p.n_pairs];
+    const int total = SECOND ? p.counters[3] : p.work_prefix[p.n_pairs];
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[0], 1);
+        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[SECOND ? 4 : 0], 1);
         __syncthreads();
-        const int item = ctl.item;
-        if (item >= total) break;
+        const int t = ctl.item;
+        if (t >= total) break;
+        const int item = SECOND ? p.dense_list[t] : t;
         const int r = run_item_fast<true, 8>(p, item, smem, gscr, ctl);
-        if (threadIdx.x == 0 && r != kItemDone) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+        if (threadIdx.x == 0) {
+            if (r == kItemToGeneral || (SECOND && r == kItemToDense)) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+            else if (r == kItemToDense) p.dense_list[atomicAdd(&p.counters[3], 1)] = item;
+        }
     }
 }
 
-void launch_k2_sparse_wide(const K2Params& p, int grid, cudaStream_t stream) {
+void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t stream) {
     static unsigned long long attr_set = 0ull;
+    const size_t fixed = k2_sparse_wide_smem_bytes(p.max_px) - (size_t)kWideWords * sizeof(uint32_t);
     if (first_use_on_device(attr_set)) {
-        cudaFuncSetAttribute(k2_sparse_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k2_sparse_wide_smem_bytes(AXB_MAX_PX));
-        cudaFuncSetAttribute(k2_sparse_wide_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k2_sparse_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(k2_sparse_wide_smem_bytes(AXB_MAX_PX) + kSparseHash * sizeof(uint32_t)));
+        cudaFuncSetAttribute(k2_sparse_wide_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(k2_sparse_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        cudaFuncSetAttribute(k2_sparse_wide_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     }
     K2Params q = p;
-    q.hash_smem = 0;
+    q.hash_smem = 1;               // two CTAs per SM leave room for the target hash in shared memory (the probe is on the wave's critical path)
     q.sparse_words = kWideWords;
-    k2_sparse_wide_kernel<<<grid, kFastThreads, k2_sparse_wide_smem_bytes(p.max_px), stream>>>(q);
+    const size_t hash_bytes = kSparseHash * sizeof(uint32_t);
+    k2_sparse_wide_kernel<false><<<grid, kFastThreads, k2_sparse_wide_smem_bytes(p.max_px) + hash_bytes, stream>>>(q);
+    // second pass: as many words as one CTA per SM can hold next to the tables, queues and hash
+    q.sparse_words = (int)(((size_t)226 * 1024 - fixed - hash_bytes) / sizeof(uint32_t)) & ~3;
+    k2_sparse_wide_kernel<true><<<grid2, kFastThreads, fixed + hash_bytes + (size_t)q.sparse_words * sizeof(uint32_t), stream>>>(q);
 }
 
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
