@@ -18,10 +18,11 @@ def test_mixin_overrides_exist_in_reference_and_compose():
     from axtrack_b200.axon_detections import B200AssociationMixin, make_drop_in, AStarPaths
     rh.load()
     Ref = sys.modules['axref.axtrack.AxonDetections'].AxonDetections
-    for name in ('detect_dataset', '_compute_detections_astar_paths', '_get_astar_path_distances'):
+    for name in ('detect_dataset', '_compute_detections_astar_paths', '_get_astar_path_distances',
+                 'get_frame_and_truedets', '_assign_IDs_to_detections'):
         assert callable(getattr(Ref, name)), name            # the reference still has what we override
         assert getattr(make_drop_in(Ref), name) is not getattr(Ref, name)
-    for name in ('get_frame_dets', 'to_cache', 'from_cache', 'assign_ids', '_assign_IDs_to_detections'):
+    for name in ('get_frame_dets', 'to_cache', 'from_cache', 'assign_ids', '_agg_all_IDed_dets', 'libmot_det2det', 'det2libmot_det'):
         assert getattr(make_drop_in(Ref), name) is getattr(Ref, name)      # inherited unchanged
 
     # the real class, real __init__ / get_frame_dets; matrices from the oracle

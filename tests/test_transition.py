@@ -42,7 +42,8 @@ def test_arc_table_matches_libmot_loop():
             c = cost[g, d]
             assert arc[g, d] == (mm.NO_ARC if c > 0.7 else int(1e5 * c))
     assert np.isinf(cost[:, 500]).all() and (arc[:, 500] == mm.NO_ARC).all()
-    with pytest.raises(NotImplementedError):
+    # a per-distance TABLE exists for weight 0 only; other weights go through transition_model (K7, tests/test_vis_sim.py)
+    with pytest.raises(ValueError):
         mm.transition_table(500, 0.6, 1, vis_sim_weight=0.2)
 
 
