@@ -1,4 +1,4 @@
-// Shared device helpers of the tile-word search kernels (axb_search_fast.cu, axb_search_pool.cu):
+// Shared device helpers of the tile-word search kernels (axb_search_fast.cu):
 // window geometry, staging of the folded sparse / dense window, predicated shared-memory
 // operations, the target probe.  See the header of axb_search_fast.cu for the layout.
 #pragma once
