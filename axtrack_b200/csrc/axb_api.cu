@@ -279,9 +279,10 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
         }
         return AXB_OK;
     }
-    // one search per CTA.  Measured alternatives (profiles/r02a_*, bit-identical results): one WARP per search 13.3 ms and
-    // two searches POOLED per CTA 13.6 ms against 12.0 ms on the config-2 block -- fewer instructions, but too few warps
-    // per SM to hide the ~6 cycles between dependent instructions; both were removed again (git history has them).
+    // one search per CTA.  Measured alternatives (profiles/r02a_*, r02p_*, bit-identical results): one WARP per search
+    // (13.3 ms; a rewrite with two entries per lane 14.3 .. 14.9 ms) and two searches POOLED per CTA (13.6 ms) against
+    // 12.1 ms on the config-2 block -- fewer instructions, but too few warps per SM to hide the latency between
+    // dependent instructions; all were removed again.
     axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
     axb::launch_k2_fast(p, std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src)), s);
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);

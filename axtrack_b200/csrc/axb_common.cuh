@@ -47,6 +47,8 @@ constexpr int kSparseCtasPerSm = 10;
 constexpr int kWideWords = 20480;     // non-zero tile words a wide sparse window can hold (80 KB; the whole diamond: 65 792)
 constexpr int kWideQCap = 384;
 constexpr int kWideSparseCtasPerSm = 2;
+constexpr int kWideHash = 1024;       // target hash of the wide sparse kernel (shared memory)
+constexpr int kWideHashMaxLoad = 512;
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists

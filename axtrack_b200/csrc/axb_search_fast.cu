@@ -81,12 +81,14 @@ enum ItemResult { kItemDone = 0, kItemToGeneral = 1, kItemToDense = 2 };
 // One work item = one source of a chain leader, processed by the whole CTA.  All control flow is
 // CTA-uniform.  kItemToGeneral: level 0 cannot answer; kItemToDense (sparse only): the window has
 // more non-zero tile words than the sparse layout holds.
-template <bool SPARSE, int LOGC = 7>
+template <bool SPARSE, int LOGC = 7, int NW = kNW>
 __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, uint32_t* gscr, Ctl& ctl) {
     using C = Cfg<SPARSE, LOGC>;
     using G = TW<LOGC>;
     static_assert(SPARSE || LOGC == 7, "the dense window exists for the 128-column circle only");
-    constexpr int NT = kFastThreads;
+    constexpr int NT = 32 * NW;
+    constexpr int kSeg = C::kQCap / NW;             // frontier entries per warp per buffer in shared memory
+    constexpr int GSEG = kFastGQCap / NW;           // ... and in the CTA's global scratch
     constexpr int HASH = C::kHash;
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
@@ -103,7 +105,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
     // (unless the launch is too small to fill the SMs: then latency counts, p.hash_smem)
     uint32_t* const hash = SPARSE && !p.hash_smem ? gscr + kCandCap + 4 * (size_t)kFastGQCap : (uint32_t*)(q0 + 2 * C::kQCap);
     uint32_t* const cand = gscr;
-    uint2* const gq0 = (uint2*)(gscr + kCandCap);          // [2][kNW][kGSeg] global overflow
+    uint2* const gq0 = (uint2*)(gscr + kCandCap);          // [2][kNW][GSEG] global overflow
     Chain& ch = ctl.ch;
 
     long long tclk = clock64();
@@ -199,8 +201,8 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
         const int ncand = ctl.ncand;
         if (ncand > 0) {
             AXB_T(0, tclk);
-            if (LOGC == 7) stage_window<SPARSE>(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, kNW);
-            else stage_window_wide(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, kNW);
+            if (LOGC == 7) stage_window<SPARSE>(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, NW);
+            else stage_window_wide(w, WIN, PB, &ctl.alloc, p.sparse_words, threadIdx.x >> 5, NW);
             __syncthreads();
             AXB_T(1, tclk);
             if (SPARSE && ctl.alloc > p.sparse_words) return kItemToDense;
@@ -226,8 +228,8 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 AXB_ASSERT(!there || widx < (SPARSE ? p.sparse_words : NR * G::TC));
                 if (there) WIN[widx] &= ~(1u << bit);
                 q0[0] = make_uint2(1u << bit, key);
-                ctl.wc[0][0] = 1; ctl.wc[0][1] = 0; ctl.wc[0][2] = 0; ctl.wc[0][3] = 0;
-                ctl.wc[1][0] = 0; ctl.wc[1][1] = 0; ctl.wc[1][2] = 0; ctl.wc[1][3] = 0;   // words of absent warps stay 0
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) { ctl.wc[0][k] = k == 0 ? 1 : 0; ctl.wc[1][k] = 0; }   // words of absent warps stay 0
             }
             __syncthreads();
 
@@ -237,6 +239,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             const uint32_t hash_s = SPARSE ? 0u : smem_u32(hash);
             const uint32_t q_s = smem_u32(q0);
             const uint32_t lastU = (uint32_t)(NR - 1);
+            const uint32_t idle_s = win_s + 4u * (uint32_t)lane;   // where a lane's claims go when it has nothing to claim (one bank per lane)
             // shared address of tile word `key` (only when want != 0); want is cleared when the
             // sparse window holds no such word
             // (sparse: PB[].y = index of the group's first word | target flags << 16, returned in aux)
@@ -254,11 +257,21 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             int unsettled = ncand;     // CTA-uniform: updated from ctl.wc[] after each barrier
             bool hit = false, defer = false;
             for (int j = 0;; ++j) {    // wave j: probe + expand the cells at hop j
-                const int4 c4 = *reinterpret_cast<const int4*>(ctl.wc[j & 1]);
-                const int p1 = c4.x & 0x7FFF, p2 = p1 + (c4.y & 0x7FFF), p3 = p2 + (c4.z & 0x7FFF);
-                const int total = p3 + (c4.w & 0x7FFF);
-                unsettled -= (c4.x >> 16) + (c4.y >> 16) + (c4.z >> 16) + (c4.w >> 16);
-                if ((c4.x | c4.y | c4.z | c4.w) & 0x8000) { defer = true; break; }   // a frontier list overflowed
+                constexpr int NWC = NW > 4 ? 8 : 4;                    // control words read: one or two 16-byte rows
+                int wcv[NWC];
+                *reinterpret_cast<int4*>(wcv) = *reinterpret_cast<const int4*>(ctl.wc[j & 1]);
+                if (NW > 4) *reinterpret_cast<int4*>(wcv + 4) = *reinterpret_cast<const int4*>(ctl.wc[j & 1] + 4);
+                int pfx[NWC + 1];                                      // pfx[k] = first entry of warp k's segment in the wave's numbering
+                pfx[0] = 0;
+                int any_ovf = 0;
+                #pragma unroll
+                for (int k = 0; k < NWC; ++k) {
+                    pfx[k + 1] = pfx[k] + (wcv[k] & 0x7FFF);
+                    unsettled -= wcv[k] >> 16;
+                    any_ovf |= wcv[k];
+                }
+                const int total = pfx[NWC];
+                if (any_ovf & 0x8000) { defer = true; break; }         // a frontier list overflowed
                 if (total == 0 || unsettled <= 0) break;
                 if (j >= RW) { hit = true; break; }                   // cells at hop == max_px exist
                 AXB_C(3, 1); AXB_C(5, total);
@@ -266,19 +279,25 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 long long tw = clock64();
 #endif
                 const uint32_t qcur_s = q_s + (uint32_t)(j & 1) * (C::kQCap * 8u);
-                const uint32_t qnxt_s = q_s + (uint32_t)((j + 1) & 1) * (C::kQCap * 8u) + (uint32_t)warp * (C::kSeg * 8u);
+                const uint32_t qnxt_s = q_s + (uint32_t)((j + 1) & 1) * (C::kQCap * 8u) + (uint32_t)warp * (kSeg * 8u);
                 int wn = 0, ws = 0;
                 bool wovf = false;
                 for (int base = warp * 32; base < total; base += NT) {
                     const int i = base + lane;
-                    const int sg = (i >= p1) + (i >= p2) + (i >= p3);
-                    const int off = i - (sg == 0 ? 0 : sg == 1 ? p1 : sg == 2 ? p2 : p3);
+                    int sg = 0, sbase = 0;                                    // whose segment entry i is in, without branches
+                    #pragma unroll
+                    for (int k = 1; k < NW; ++k) {
+                        const bool ge = i >= pfx[k];
+                        sg += (int)ge;
+                        sbase = ge ? pfx[k] : sbase;
+                    }
+                    const int off = i - sbase;
                     const bool act = i < total;
-                    AXB_ASSERT(!act || (sg < kNW && off >= 0 && off < C::kSeg + kGSeg));
-                    uint2 e = lds64_if(qcur_s + 8u * (uint32_t)(sg * C::kSeg + off), act && off < C::kSeg);
-                    if (__any_sync(kFull, act && off >= C::kSeg)) {           // entries that spilled to global memory
-                        if (act && off >= C::kSeg)
-                            e = (gq0 + (size_t)(j & 1) * kFastGQCap)[(size_t)sg * kGSeg + (off - C::kSeg)];
+                    AXB_ASSERT(!act || (sg < NW && off >= 0 && off < kSeg + GSEG));
+                    uint2 e = lds64_if(qcur_s + 8u * (uint32_t)(sg * kSeg + off), act && off < kSeg);
+                    {                                                         // entries that spilled to global memory
+                        const uint2 eg = ldg64_if(gq0 + (size_t)(j & 1) * kFastGQCap + (size_t)sg * GSEG + (off - kSeg), act && off >= kSeg);
+                        e.x |= eg.x; e.y |= eg.y;
                     }
                     const uint32_t f = e.x, k0 = e.y;
                     // candidates: cells of the word itself, of the right / left / lower / upper word
@@ -309,11 +328,11 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const uint32_t o2 = lds_if(a2, cd2) & cd2;
                     const uint32_t o3 = lds_if(a3, cd3) & cd3;
                     const uint32_t o4 = lds_if(a4, cd4) & cd4;
-                    const uint32_t c0 = claim_if(a0, o0);
-                    const uint32_t c1 = claim_if(a1, o1);
-                    const uint32_t c2 = claim_if(a2, o2);
-                    const uint32_t c3 = claim_if(a3, o3);
-                    const uint32_t c4c = claim_if(a4, o4);
+                    const uint32_t c0 = claim_if(a0, o0, idle_s);
+                    const uint32_t c1 = claim_if(a1, o1, idle_s);
+                    const uint32_t c2 = claim_if(a2, o2, idle_s);
+                    const uint32_t c3 = claim_if(a3, o3, idle_s);
+                    const uint32_t c4c = claim_if(a4, o4, idle_s);
                     // targets among the cells being expanded (hop j, path length j + 1)
                     if (__any_sync(kFull, maybe)) {
                         int ns = 0;
@@ -325,33 +344,35 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const uint32_t b2 = __ballot_sync(kFull, c2 != 0u), b3 = __ballot_sync(kFull, c3 != 0u);
                     const uint32_t b4 = __ballot_sync(kFull, c4c != 0u);
                     const int tot = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3) + __popc(b4);
-                    if (tot) {
-                        int slot = wn + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
-                        AXB_ASSERT(slot >= 0 && (wn + tot > C::kSeg + kGSeg || slot + (c0 != 0u) + (c1 != 0u) + (c2 != 0u) + (c3 != 0u) + (c4c != 0u) <= wn + tot));
-                        if (wn + tot <= C::kSeg) {
-                            uint32_t sa = qnxt_s + 8u * (uint32_t)slot;
-                            sts64_if(sa, c0, k0, c0);   sa += c0 ? 8u : 0u;
-                            sts64_if(sa, c1, k1, c1);   sa += c1 ? 8u : 0u;
-                            sts64_if(sa, c2, k2, c2);   sa += c2 ? 8u : 0u;
-                            sts64_if(sa, c3, k3, c3);   sa += c3 ? 8u : 0u;
-                            sts64_if(sa, c4c, k4, c4c);
-                        } else if (wn + tot <= C::kSeg + kGSeg) {
+                    int slot = wn + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
+                    AXB_ASSERT(slot >= 0 && (wn + tot > kSeg + GSEG || slot + (c0 != 0u) + (c1 != 0u) + (c2 != 0u) + (c3 != 0u) + (c4c != 0u) <= wn + tot));
+                    const uint32_t fits = wn + tot <= kSeg ? 1u : 0u;     // warp-uniform; the stores are predicated, not branched over
+                    {
+                        uint32_t sa = qnxt_s + 8u * (uint32_t)slot;
+                        sts64_if(sa, c0, k0, fits ? c0 : 0u);   sa += c0 ? 8u : 0u;
+                        sts64_if(sa, c1, k1, fits ? c1 : 0u);   sa += c1 ? 8u : 0u;
+                        sts64_if(sa, c2, k2, fits ? c2 : 0u);   sa += c2 ? 8u : 0u;
+                        sts64_if(sa, c3, k3, fits ? c3 : 0u);   sa += c3 ? 8u : 0u;
+                        sts64_if(sa, c4c, k4, fits ? c4c : 0u);
+                    }
+                    if (!fits) {                                              // rare: the tail of the segment lives in global memory
+                        if (wn + tot <= kSeg + GSEG) {
                             const uint32_t cc[5] = {c0, c1, c2, c3, c4c};
                             const uint32_t kk[5] = {k0, k1, k2, k3, k4};
-                            uint2* const gnxt = gq0 + (size_t)((j + 1) & 1) * kFastGQCap + (size_t)warp * kGSeg;
+                            uint2* const gnxt = gq0 + (size_t)((j + 1) & 1) * kFastGQCap + (size_t)warp * GSEG;
                             #pragma unroll
                             for (int d = 0; d < 5; ++d) {
                                 if (cc[d]) {
-                                    if (slot < C::kSeg) sts64_if(qnxt_s + 8u * (uint32_t)slot, cc[d], kk[d], 1u);
-                                    else gnxt[slot - C::kSeg] = make_uint2(cc[d], kk[d]);
+                                    if (slot < kSeg) sts64_if(qnxt_s + 8u * (uint32_t)slot, cc[d], kk[d], 1u);
+                                    else gnxt[slot - kSeg] = make_uint2(cc[d], kk[d]);
                                     ++slot;
                                 }
                             }
                         } else {
                             wovf = true;
                         }
-                        wn += tot;
                     }
+                    wn += tot;
                 }
                 if (lane == 0) ctl.wc[(j + 1) & 1][warp] = wovf ? 0x8000 : (wn | (ws << 16));
                 AXB_T(6, tw);
@@ -415,7 +436,7 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
 // whose window holds more go to the dense list.  Second pass (SECOND = true): those items with windows of up to
 // kWideWords2 words, 1 CTA per SM.  What neither holds (e.g. an all-ones mask: 65 792 words) goes to the all-levels kernel.
 template <bool SECOND>
-__global__ void __launch_bounds__(kFastThreads, SECOND ? 1 : kWideSparseCtasPerSm) k2_sparse_wide_kernel(const K2Params p) {
+__global__ void __launch_bounds__(32 * kWideNW, SECOND ? 1 : kWideSparseCtasPerSm) k2_sparse_wide_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
@@ -427,7 +448,7 @@ __global__ void __launch_bounds__(kFastThreads, SECOND ? 1 : kWideSparseCtasPerS
         const int t = ctl.item;
         if (t >= total) break;
         const int item = SECOND ? p.dense_list[t] : t;
-        const int r = run_item_fast<true, 8>(p, item, smem, gscr, ctl);
+        const int r = run_item_fast<true, 8, kWideNW>(p, item, smem, gscr, ctl);
         if (threadIdx.x == 0) {
             if (r == kItemToGeneral || (SECOND && r == kItemToDense)) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
             else if (r == kItemToDense) p.dense_list[atomicAdd(&p.counters[3], 1)] = item;
@@ -439,7 +460,7 @@ void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t 
     static unsigned long long attr_set = 0ull;
     const size_t fixed = k2_sparse_wide_smem_bytes(p.max_px) - (size_t)kWideWords * sizeof(uint32_t);
     if (first_use_on_device(attr_set)) {
-        cudaFuncSetAttribute(k2_sparse_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(k2_sparse_wide_smem_bytes(AXB_MAX_PX) + kSparseHash * sizeof(uint32_t)));
+        cudaFuncSetAttribute(k2_sparse_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(k2_sparse_wide_smem_bytes(AXB_MAX_PX) + kWideHash * sizeof(uint32_t)));
         cudaFuncSetAttribute(k2_sparse_wide_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(k2_sparse_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
         cudaFuncSetAttribute(k2_sparse_wide_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -447,11 +468,11 @@ void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t 
     K2Params q = p;
     q.hash_smem = 1;               // two CTAs per SM leave room for the target hash in shared memory (the probe is on the wave's critical path)
     q.sparse_words = kWideWords;
-    const size_t hash_bytes = kSparseHash * sizeof(uint32_t);
-    k2_sparse_wide_kernel<false><<<grid, kFastThreads, k2_sparse_wide_smem_bytes(p.max_px) + hash_bytes, stream>>>(q);
+    const size_t hash_bytes = kWideHash * sizeof(uint32_t);
+    k2_sparse_wide_kernel<false><<<grid, 32 * kWideNW, k2_sparse_wide_smem_bytes(p.max_px) + hash_bytes, stream>>>(q);
     // second pass: as many words as one CTA per SM can hold next to the tables, queues and hash
     q.sparse_words = (int)(((size_t)226 * 1024 - fixed - hash_bytes) / sizeof(uint32_t)) & ~3;
-    k2_sparse_wide_kernel<true><<<grid2, kFastThreads, fixed + hash_bytes + (size_t)q.sparse_words * sizeof(uint32_t), stream>>>(q);
+    k2_sparse_wide_kernel<true><<<grid2, 32 * kWideNW, fixed + hash_bytes + (size_t)q.sparse_words * sizeof(uint32_t), stream>>>(q);
 }
 
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {

@@ -73,7 +73,7 @@ struct Chain {
 struct __align__(16) Ctl {
     // per-warp (entries appended | overflow << 15 | targets reached << 16) of the last wave, double
     // buffered: wave s reads wc[s&1], every warp stores its own word of wc[(s+1)&1] at its end
-    int wc[2][4];
+    int wc[2][8];
     Chain ch;
     int ncand;
     int item;
@@ -144,19 +144,21 @@ namespace {
 
 constexpr int kNW = kFastThreads / 32;            // warps per search
 constexpr int kGSeg = kFastGQCap / kNW;           // global overflow entries per warp per buffer
-static_assert(kNW >= 1 && kNW <= 4, "Ctl::wc holds one word per warp in one 16-byte row");
+constexpr int kWideNW = 8;                        // warps per search of the 256-column kernels (about 100 entries per wave, 2 CTAs per SM)
+static_assert(kNW >= 1 && kNW <= 4 && kWideNW <= 8, "Ctl::wc holds one word per warp in one / two 16-byte rows");
 
 template <bool SPARSE, int LOGC = 7> struct Cfg;
 template <> struct Cfg<false, 7> {
-    static constexpr int kQCap = kFastQCap, kSeg = kFastQCap / kNW, kHash = kHashSize, kMaxLoad = kHashMaxLoad;
+    static constexpr int kQCap = kFastQCap, kHash = kHashSize, kMaxLoad = kHashMaxLoad;
 };
 template <> struct Cfg<true, 7> {
-    static constexpr int kQCap = kSparseQCap, kSeg = kSparseQCap / kNW, kHash = kSparseHash, kMaxLoad = kSparseHashMaxLoad;
+    static constexpr int kQCap = kSparseQCap, kHash = kSparseHash, kMaxLoad = kSparseHashMaxLoad;
 };
-template <> struct Cfg<true, 8> {      // max_px 512 .. 1023: about twice the frontier entries per wave
-    static constexpr int kQCap = kWideQCap, kSeg = kWideQCap / kNW, kHash = kSparseHash, kMaxLoad = kSparseHashMaxLoad;
+template <> struct Cfg<true, 8> {      // max_px 512 .. 1023: about twice the frontier entries per wave and four times the in-range targets
+    static constexpr int kQCap = kWideQCap, kHash = kWideHash, kMaxLoad = kWideHashMaxLoad;
 };
-static_assert(kFastQCap / kNW + kGSeg < 0x8000 && kWideQCap / kNW + kGSeg < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
+static_assert(kFastQCap / kNW + kGSeg < 0x8000 && kWideQCap / kWideNW + kFastGQCap / kWideNW < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
+static_assert(kWideHashMaxLoad <= (1 << TW<8>::SLOTB) && kWideHashMaxLoad <= kCandCap, "wide hash entries keep 9 bits of candidate slot");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -175,13 +177,23 @@ __device__ __forceinline__ uint2 lds64_if(uint32_t a, uint32_t want) {
                  : "=r"(v.x), "=r"(v.y) : "r"(a), "r"(want) : "memory");
     return v;
 }
-// clear the bits `o` of the word at shared address `a`; returns those of them this thread cleared
-__device__ __forceinline__ uint32_t claim_if(uint32_t a, uint32_t o) {
+// clear the bits `o` of the word at shared address `a`; returns those of them this thread cleared.  With o == 0 the
+// atomic goes to `idle` (any valid shared word: AND with all ones changes nothing) -- ptxas turns a predicated
+// atom.shared into a branch with a reconvergence point, and a lone branch costs a warp ~13 issue cycles
+// (ncu source view, stall_branch_resolving), five of them per frontier entry.
+__device__ __forceinline__ uint32_t claim_if(uint32_t a, uint32_t o, uint32_t idle) {
     uint32_t old;
-    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 n;\n\tsetp.ne.u32 p, %2, 0;\n\tnot.b32 n, %2;\n\tmov.u32 %0, 0;\n\t"
-                 "@p atom.shared.and.b32 %0, [%1], n;\n\t}"
-                 : "=r"(old) : "r"(a), "r"(o) : "memory");
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 n, b;\n\tsetp.ne.u32 p, %2, 0;\n\tnot.b32 n, %2;\n\tselp.b32 b, %1, %3, p;\n\t"
+                 "atom.shared.and.b32 %0, [b], n;\n\t}"
+                 : "=r"(old) : "r"(a), "r"(o), "r"(idle) : "memory");
     return old & o;
+}
+// value at global address `p`, or 0 when want == 0
+__device__ __forceinline__ uint2 ldg64_if(const uint2* p, uint32_t want) {
+    uint2 v;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\tmov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\t@p ld.global.v2.u32 {%0, %1}, [%2];\n\t}"
+                 : "=r"(v.x), "=r"(v.y) : "l"(p), "r"(want) : "memory");
+    return v;
 }
 __device__ __forceinline__ void sts64_if(uint32_t a, uint32_t x, uint32_t y, uint32_t want) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.shared.v2.u32 [%0], {%1, %2};\n\t}"
