@@ -27,7 +27,7 @@ SYMBOLS = ('axb_create', 'axb_destroy', 'axb_last_error', 'axb_version', 'axb_la
            'axb_cost_matrix', 'axb_cost_matrix_batch_host', 'axb_cost_matrix_host',
            'axb_decode_nms', 'axb_decode_nms_host', 'axb_transition_cost_batch', 'axb_trace_paths', 'axb_feature_hist',
            'axb_feature_hist_frames', 'axb_vis_sim',
-           'axb_tile_nonempty', 'axb_gather_frametiles', 'axb_stitched_frame', 'axb_status')
+           'axb_tile_nonempty', 'axb_tile_nonempty_noalloc', 'axb_gather_frametiles', 'axb_stitched_frame', 'axb_status')
 
 
 class PairDesc(ctypes.Structure):
@@ -96,6 +96,8 @@ def load():
     L.axb_vis_sim.argtypes = [vp, vp, ci, vp, ci, ci, vp, ci, vp, vp]
     L.axb_tile_nonempty.restype = ci
     L.axb_tile_nonempty.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp]
+    L.axb_tile_nonempty_noalloc.restype = ci
+    L.axb_tile_nonempty_noalloc.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp]
     L.axb_gather_frametiles.restype = ci
     L.axb_gather_frametiles.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, ci, vp, ci, ci, ci, ci, vp, vp]
     L.axb_stitched_frame.restype = ci

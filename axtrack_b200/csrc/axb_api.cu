@@ -664,6 +664,26 @@ int axb_tile_nonempty(axb_ctx* c, const float* X_dev, int T, int C, int H, int W
     return AXB_OK;
 }
 
+// No cudaMalloc / cudaFree on this path: the vote flags live in a static device array of axb_tiles.cu.
+int axb_tile_nonempty_noalloc(axb_ctx* c, const float* X_dev, int T, int C, int H, int W, int tilesize, uint8_t* nonempty_dev,
+                              void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (T < 0 || C < 1 || H <= 0 || W <= 0 || tilesize < 1 || T > 65535) return bad_arg(c, "axb_tile_nonempty_noalloc: bad size");
+    if (T == 0) return AXB_OK;
+    if (!X_dev || !nonempty_dev) return bad_arg(c, "axb_tile_nonempty_noalloc: NULL pointer");
+    const unsigned long long n_flags = (unsigned long long)((H + tilesize - 1) / tilesize) * ((W + tilesize - 1) / tilesize) * T;
+    if (n_flags > (unsigned long long)AXB_NOALLOC_MAX_TILE_FRAMES) {
+        char buf[200];
+        snprintf(buf, sizeof buf, "axb_tile_nonempty_noalloc: ytiles * xtiles * T = %llu exceeds AXB_NOALLOC_MAX_TILE_FRAMES = %d "
+                 "(use axb_tile_nonempty, or fewer frames per call)", n_flags, AXB_NOALLOC_MAX_TILE_FRAMES);
+        return bad_arg(c, buf);
+    }
+    AXB_ON_DEVICE(c);
+    AXB_CUDA(c, axb::launch_k6_nonempty_static(X_dev, T, C, H, W, tilesize, nonempty_dev, (cudaStream_t)stream));
+    c->launches += 2;
+    return AXB_OK;
+}
+
 int axb_gather_frametiles(axb_ctx* c, const float* X_dev, int T, int C, int H, int W, int tilesize,
                           const int32_t* tile_yx_dev, int ntiles, const int32_t* frames_dev, int n_frames,
                           int temporal_context, int chan_lo, int chan_n, float* out_dev, void* stream) {

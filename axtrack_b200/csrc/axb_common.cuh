@@ -144,6 +144,7 @@ void launch_k7(const float* f_src, int n_src, const float* f_dst, int n_dst, int
 
 constexpr int kK6FlagStride = 8;      // uint32 words between two K6 vote flags: one flag per 32-byte sector
 void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint32_t* flags, uint8_t* nonempty, cudaStream_t stream);
+cudaError_t launch_k6_nonempty_static(const float* X, int T, int C, int H, int W, int ts, uint8_t* nonempty, cudaStream_t stream);   // flags in a static device array
 void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,
                       const int32_t* frames, int B, int tc, int chan_lo, int nch, float* out,
                       unsigned long long* err_flags, int n_sms, cudaStream_t stream);

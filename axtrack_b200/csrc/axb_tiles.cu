@@ -14,6 +14,7 @@
 #include "axb_common.cuh"
 #include <cuda.h>          // CUtensorMap + the prototype of cuTensorMapEncodeTiled (resolved at run time, no -lcuda)
 #include <algorithm>
+#include <mutex>
 
 namespace axb {
 
@@ -287,6 +288,36 @@ void launch_k6_nonempty(const float* X, int T, int C, int H, int W, int ts, uint
     if (vec) k6_nonempty_kernel<true><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, flags);
     else k6_nonempty_kernel<false><<<grid, 256, 0, stream>>>(X, T, C, H, W, ts, xtiles, flags);
     k6_flags_to_bytes_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(flags, n, nonempty);
+}
+
+// ---- axb_tile_nonempty_noalloc: the same two kernels with the vote flags in a file-scope device array ----------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, serving loops, harnesses that forbid it).  Every GPU that loads the
+// library holds the array (kK6StaticMaxFlags * 32 B = 2 MiB) until the process exits.  All calls on a device share
+// it: launch_k6_nonempty zeroes the flags of the call first, and calls that overlap on the GPU race.
+static __device__ __align__(256) uint32_t g_k6_static_flags[(size_t)AXB_NOALLOC_MAX_TILE_FRAMES * kK6FlagStride];
+
+// Host code must not pass g_k6_static_flags itself to a kernel (there the name is a host-side stand-in, not a
+// device address): the device address is looked up once per device, with that device current.
+cudaError_t launch_k6_nonempty_static(const float* X, int T, int C, int H, int W, int ts, uint8_t* nonempty, cudaStream_t stream) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static uint32_t* flags_of_device[kMaxDev] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    uint32_t* flags = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (dev >= 0 && dev < kMaxDev) flags = flags_of_device[dev];
+        if (!flags) {
+            e = cudaGetSymbolAddress((void**)&flags, g_k6_static_flags);
+            if (e != cudaSuccess) return e;
+            if (dev >= 0 && dev < kMaxDev) flags_of_device[dev] = flags;
+        }
+    }
+    launch_k6_nonempty(X, T, C, H, W, ts, flags, nonempty, stream);     // cudaMemsetAsync of this call's flags + 2 kernels
+    return cudaGetLastError();
 }
 
 void launch_k6_gather(const float* X, int T, int C, int H, int W, int ts, const int32_t* tile_yx, int ntiles,

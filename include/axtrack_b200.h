@@ -240,6 +240,19 @@ int axb_vis_sim(axb_ctx* ctx, const float* feats_src_dev, int n_src, const float
  * (its planes are written as zeros). */
 int axb_tile_nonempty(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
                       uint8_t* nonempty_dev, void* stream);
+/* axb_tile_nonempty without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and result as axb_tile_nonempty; the per-(tile, frame) vote flags
+ * live in a static device array of the library instead of the ctx's grown scratch, so
+ *   - ytiles * xtiles * T must be <= AXB_NOALLOC_MAX_TILE_FRAMES, else AXB_ERR_BAD_ARG (axb_last_error says so);
+ *   - every GPU that loads the library holds that array (AXB_NOALLOC_MAX_TILE_FRAMES * 32 B = 2 MiB) until exit;
+ *   - all calls on one device share it (any ctx, any stream): each call zeroes its flags first, and two calls
+ *     that overlap on the GPU race -- order them on one stream or with events;
+ *   - the call does no cudaMalloc / cudaFree / allocating library routine; the first call on a device looks the
+ *     array's device address up (cudaGetSymbolAddress), so make one call per device before a graph capture. */
+#define AXB_NOALLOC_MAX_TILE_FRAMES 65536
+int axb_tile_nonempty_noalloc(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
+                              uint8_t* nonempty_dev, void* stream);
 int axb_gather_frametiles(axb_ctx* ctx, const float* X_dev, int T, int C, int H, int W, int tilesize,
                           const int32_t* tile_yx_dev, int ntiles, const int32_t* frames_dev, int n_frames,
                           int temporal_context, int chan_lo, int chan_n, float* out_dev, void* stream);
