@@ -33,7 +33,12 @@ struct axb_ctx {
     int* counters = nullptr;
     int* prefix_dev = nullptr;        int prefix_cap = 0;   int last_n_pairs = 0;   // [work | all | next] x prefix_cap
     int* gen_list = nullptr;          size_t gen_list_bytes = 0;
-    int* dense_list = nullptr;        size_t dense_list_bytes = 0;
+    int* dense_list = nullptr;        size_t dense_list_bytes = 0;      // [2][total_src]: windows the first / the directed pass could not hold
+    int* dir_list = nullptr;          size_t dir_list_bytes = 0;        // work items that need a directed search after the cover pass
+    uint32_t* item_bits = nullptr;    size_t item_bits_bytes = 0;
+    int* comp_label = nullptr;        size_t comp_label_bytes = 0;      // mask components (axb_components.cu)
+    int4* comp_ext = nullptr;         size_t comp_ext_bytes = 0;
+    int dense_stride = 0;
     uint8_t* trace_par = nullptr;                                      // K4: per general CTA entry directions
     int* trace_iota = nullptr;        size_t trace_iota_bytes = 0;
     uint32_t* k2_tiles = nullptr;     size_t k2_tiles_bytes = 0;       // 8x4-pixel tile words of the masks of the current call
@@ -103,11 +108,37 @@ int ensure_k2(axb_ctx* c, int n_pairs, int total_src) {
         if (c->prefix_dev) AXB_CUDA(c, cudaFree(c->prefix_dev));
         c->prefix_dev = nullptr;
         c->prefix_cap = std::max(n_pairs + 1, 1024) * 2;
-        AXB_CUDA(c, cudaMalloc((void**)&c->prefix_dev, 3 * (size_t)c->prefix_cap * sizeof(int)));
+        AXB_CUDA(c, cudaMalloc((void**)&c->prefix_dev, axb::kPrepArrays * (size_t)c->prefix_cap * sizeof(int)));
     }
-    int rc = grow(c, &c->dense_list, &c->dense_list_bytes, (size_t)std::max(total_src, 1) * sizeof(int));
+    const size_t n_items = (size_t)std::max(total_src, 1);
+    int rc = grow(c, &c->dense_list, &c->dense_list_bytes, 2 * n_items * sizeof(int));
     if (rc != AXB_OK) return rc;
-    return grow(c, &c->gen_list, &c->gen_list_bytes, (size_t)std::max(total_src, 1) * sizeof(int));
+    c->dense_stride = (int)(c->dense_list_bytes / (2 * sizeof(int)));
+    if ((rc = grow(c, &c->dir_list, &c->dir_list_bytes, n_items * sizeof(int))) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->item_bits, &c->item_bits_bytes, (n_items + 31) / 32 * sizeof(uint32_t))) != AXB_OK) return rc;
+    return grow(c, &c->gen_list, &c->gen_list_bytes, n_items * sizeof(int));
+}
+
+axb::K2Prep prep_arrays(axb_ctx* c) {
+    axb::K2Prep o;
+    int* const b = c->prefix_dev;
+    const size_t n = (size_t)c->prefix_cap;
+    o.work_prefix = b; o.all_prefix = b + n; o.next_same = b + 2 * n; o.p1_prefix = b + 3 * n; o.rev_head = b + 4 * n;
+    o.rev_next = b + 5 * n; o.lead_of = b + 6 * n; o.dst_head = b + 7 * n; o.state = b + 8 * n;
+    o.item_bits = c->item_bits;
+    return o;
+}
+
+void set_prep(axb::K2Params& p, const axb::K2Prep& o, axb_ctx* c) {
+    p.work_prefix = o.work_prefix; p.all_prefix = o.all_prefix; p.next_same = o.next_same; p.p1_prefix = o.p1_prefix;
+    p.rev_head = o.rev_head; p.rev_next = o.rev_next; p.lead_of = o.lead_of; p.item_bits = o.item_bits;
+    p.dir_list = c->dir_list; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.counters = c->counters;
+}
+
+// where a fast-kernel launch takes its items from / puts the windows it cannot hold
+void set_source(axb::K2Params& p, const int* list, int len_ctr, int ticket_ctr, int* dense_out, int dense_out_ctr, int reverse) {
+    p.src_list = list; p.src_len_ctr = len_ctr; p.src_ticket_ctr = ticket_ctr;
+    p.dense_out = dense_out; p.dense_out_ctr = dense_out_ctr; p.reverse = reverse;
 }
 
 }  // namespace
@@ -149,7 +180,7 @@ void axb_destroy(axb_ctx* c) {
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
     cudaFree(c->trace_par); cudaFree(c->trace_iota); cudaFree(c->k2_wide_scratch); cudaFree(c->trace_par_wide);
-    cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
+    cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->dir_list); cudaFree(c->item_bits); cudaFree(c->comp_label); cudaFree(c->comp_ext); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
     cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1); cudaFree(c->k6_flags);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -243,39 +274,71 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     if (wide && !c->k2_wide_scratch)
         AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kWideCtasPerSm * axb::kGenScratchWordsWide * sizeof(uint32_t)));
     axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
-    int* const work_prefix = c->prefix_dev;
-    int* const all_prefix = c->prefix_dev + c->prefix_cap;
-    int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
-    axb::launch_k2_prep(pairs_dev, n_pairs, work_prefix, all_prefix, next_same, c->counters, n_masks, n_dets,
-                        (long long)out_capacity, total_src, c->status_dev + 1, s);
+    // Cover (axb_search.cu k2_prep_kernel): pairs whose source frame is not searched are answered from their target
+    // side; that needs the components of the masks.  Off for a single pair (nothing to share), for label arrays
+    // beyond 4 GiB and with AXB_K2_NO_REVERSE (A/B timing, tests).
+    static const bool no_reverse = getenv("AXB_K2_NO_REVERSE") != nullptr;
+    const size_t px = (size_t)n_masks * H * W;
+    const bool cover = !no_reverse && n_pairs >= 2 && (size_t)H * W < (1ull << 31) && px * 20 <= (4ull << 30);
+    if (cover) {
+        if ((rc = grow(c, &c->comp_label, &c->comp_label_bytes, px * sizeof(int))) != AXB_OK) return rc;
+        if ((rc = grow(c, &c->comp_ext, &c->comp_ext_bytes, px * sizeof(int4))) != AXB_OK) return rc;
+        axb::launch_k2_components(mask_bits_dev, n_masks, H, W, Wp, c->comp_label, c->comp_ext, s);
+        c->launches += 4;
+    }
+    const axb::K2Prep prep = prep_arrays(c);
+    axb::launch_k2_prep(pairs_dev, n_pairs, prep, c->counters, n_masks, n_dets, (long long)out_capacity, total_src, cover ? 1 : 0,
+                        c->status_dev + 1, s);
     c->last_n_pairs = n_pairs;
     axb::K2Params p;
+    memset(&p, 0, sizeof p);
     p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = Wp;
     p.mask_tiles = c->k2_tiles; p.TH = TH; p.TWp = 4 * Wp;
     p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs;
-    p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
+    set_prep(p, prep, c);
     p.max_px = max_px; p.hash_smem = 0; p.sparse_words = axb::kSparseWords; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = wide ? c->k2_wide_scratch : c->k2_gen_scratch;
-    p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
+    p.err_key = c->status_dev;
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
     p.orig_base = orig_base;
+    p.comp_label = cover ? c->comp_label : nullptr; p.comp_ext = cover ? c->comp_ext : nullptr;
+    int* const dense_a = c->dense_list;
+    int* const dense_b = c->dense_list + c->dense_stride;
+    // The launches of a call: (1) level-0 search from every detection of the searched sets, with the reverse members of
+    // their chains; (2) the windows (1) could not hold; (3) directed searches for the detections of the other sets that
+    // (1) and (2) could not answer from the target side (none on connected masks); (4) the windows (3) could not hold;
+    // (5) all levels for what level 0 cannot answer.
     if (wide) {
-        // max_px 512 .. 1023: sparse tile-word windows on the 256-column circle first (level 0, 2 CTAs per SM); what they
-        // cannot hold or answer goes to the all-levels kernel with its bitmaps in global memory.  AXB_K2_WIDE_GENERAL_ONLY
-        // (round-1 behaviour, for A/B timing): every source on the all-levels kernel.
+        // max_px 512 .. 1023: sparse tile-word windows on the 256-column circle (level 0, 2 CTAs per SM, then 1 CTA per SM
+        // for the windows that did not fit); what they cannot hold or answer goes to the all-levels kernel with its bitmaps
+        // in global memory.  AXB_K2_WIDE_GENERAL_ONLY (round-1 behaviour, for A/B timing): every source on that kernel.
         static const bool general_only = getenv("AXB_K2_WIDE_GENERAL_ONLY") != nullptr;
-        if (general_only) axb::launch_k2_all_to_general(work_prefix, n_pairs, c->gen_list, c->counters, s);
-        else axb::launch_k2_sparse_wide(p, std::max(1, std::min(c->num_sms * axb::kWideSparseCtasPerSm, total_src)),
-                                        std::max(1, std::min(c->num_sms, total_src)), s);
+        const int g1 = std::max(1, std::min(c->num_sms * axb::kWideSparseCtasPerSm, total_src));
+        const int g2 = std::max(1, std::min(c->num_sms, total_src));
+        if (general_only) axb::launch_k2_all_to_general(prep.work_prefix, n_pairs, c->gen_list, c->counters, s);
+        else {
+            set_source(p, nullptr, 0, axb::kCtrP1Ticket, dense_a, axb::kCtrDenseALen, cover ? 1 : 0);
+            axb::launch_k2_sparse_wide(p, g1, false, s);
+            set_source(p, dense_a, axb::kCtrDenseALen, axb::kCtrDenseATicket, nullptr, 0, cover ? 1 : 0);
+            axb::launch_k2_sparse_wide(p, g2, true, s);
+            if (cover) {
+                set_source(p, c->dir_list, axb::kCtrDirLen, axb::kCtrDirTicket, dense_b, axb::kCtrDenseBLen, 0);
+                axb::launch_k2_sparse_wide(p, g1, false, s);
+                set_source(p, dense_b, axb::kCtrDenseBLen, axb::kCtrDenseBTicket, nullptr, 0, 0);
+                axb::launch_k2_sparse_wide(p, g2, true, s);
+                c->launches += 2;
+            }
+        }
         axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * axb::kWideCtasPerSm, total_src)), s);
         c->launches += 5;
         AXB_CUDA(c, cudaGetLastError());
         static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;     // profiling aid: where the work items went
         if (dbg) {
-            int h[8];
+            int h[16];
             cudaStreamSynchronize(s);
             cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
-            fprintf(stderr, "[axb] wide K2: %d sources, %d to the second pass, %d to the all-levels kernel\n", total_src, h[3], h[1]);
+            fprintf(stderr, "[axb] wide K2: %d sources, %d searched in the first pass, %d to the second kind, %d directed, %d to the all-levels kernel\n",
+                    total_src, h[0], h[3], h[5], h[1]);
         }
         return AXB_OK;
     }
@@ -283,11 +346,30 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     // (13.3 ms; a rewrite with two entries per lane 14.3 .. 14.9 ms) and two searches POOLED per CTA (13.6 ms) against
     // 12.1 ms on the config-2 block -- fewer instructions, but too few warps per SM to hide the latency between
     // dependent instructions; all were removed again.
-    axb::launch_k2_sparse(p, std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src)), s);
-    axb::launch_k2_fast(p, std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src)), s);
+    const int gs = std::max(1, std::min(c->num_sms * axb::kSparseCtasPerSm, total_src));
+    const int gd = std::max(1, std::min(c->num_sms * axb::kFastCtasPerSm, total_src));
+    set_source(p, nullptr, 0, axb::kCtrP1Ticket, dense_a, axb::kCtrDenseALen, cover ? 1 : 0);
+    axb::launch_k2_sparse(p, gs, s);
+    set_source(p, dense_a, axb::kCtrDenseALen, axb::kCtrDenseATicket, nullptr, 0, cover ? 1 : 0);
+    axb::launch_k2_fast(p, gd, s);
+    if (cover) {
+        set_source(p, c->dir_list, axb::kCtrDirLen, axb::kCtrDirTicket, dense_b, axb::kCtrDenseBLen, 0);
+        axb::launch_k2_sparse(p, gs, s);
+        set_source(p, dense_b, axb::kCtrDenseBLen, axb::kCtrDenseBTicket, nullptr, 0, 0);
+        axb::launch_k2_fast(p, gd, s);
+        c->launches += 2;
+    }
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
     c->launches += 5;
     AXB_CUDA(c, cudaGetLastError());
+    static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;
+    if (dbg) {
+        int h[16];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[axb] K2: %d sources, %d searched in the first pass, %d dense windows, %d directed (+%d dense), %d to the all-levels kernel\n",
+                total_src, h[0], h[3], h[5], h[7], h[1]);
+    }
     return AXB_OK;
 }
 
@@ -574,11 +656,8 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     if ((rc = grow(c, &c->st_unr, &c->st_unr_bytes, (size_t)n_req)) != AXB_OK) return rc;
     AXB_CUDA(c, cudaMemcpyAsync(c->st_dets, dets.data(), dets.size() * 4, cudaMemcpyHostToDevice, s));      // pageable: staged before return
     AXB_CUDA(c, cudaMemcpyAsync(c->st_pairs, pairs.data(), pairs.size() * sizeof(axb_pair_desc), cudaMemcpyHostToDevice, s));
-    int* const work_prefix = c->prefix_dev;
-    int* const all_prefix = c->prefix_dev + c->prefix_cap;
-    int* const next_same = c->prefix_dev + 2 * (size_t)c->prefix_cap;
-    axb::launch_k2_prep(c->st_pairs, n_req, work_prefix, all_prefix, next_same, c->counters, n_masks, 2 * n_req, n_req,
-                        n_req, c->status_dev + 1, s);
+    const axb::K2Prep prep = prep_arrays(c);
+    axb::launch_k2_prep(c->st_pairs, n_req, prep, c->counters, n_masks, 2 * n_req, n_req, n_req, 0, c->status_dev + 1, s);
     c->last_n_pairs = n_req;
     // every request goes straight to the all-levels kernel: gen_list = 0 .. n-1, counters[1] = n
     AXB_CUDA(c, cudaMemcpyAsync(c->gen_list, iota.data(), (size_t)n_req * sizeof(int), cudaMemcpyHostToDevice, s));
@@ -587,10 +666,10 @@ int axb_trace_paths(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int 
     memset(&p, 0, sizeof p);
     p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = (W + 31) / 32;
     p.dets_yx = c->st_dets; p.pairs = c->st_pairs; p.n_pairs = n_req;
-    p.work_prefix = work_prefix; p.all_prefix = all_prefix; p.next_same = next_same;
+    set_prep(p, prep, c);
     p.max_px = max_px; p.path_len = c->st_plen; p.unreachable = c->st_unr; p.wcost = nullptr;
     p.fast_scratch = c->k2_fast_scratch; p.gen_scratch = wide ? c->k2_wide_scratch : c->k2_gen_scratch;
-    p.counters = c->counters; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.err_key = c->status_dev;
+    p.err_key = c->status_dev;
     p.trace_par = wide ? c->trace_par_wide : c->trace_par; p.trace_yx = path_yx_dev; p.trace_len = path_len_dev;
     axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * (wide ? axb::kWideCtasPerSm : 1), n_req)), s);
     c->launches += 2;

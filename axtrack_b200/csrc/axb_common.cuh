@@ -18,7 +18,9 @@ namespace axb {
 // bitmap at max_px = 500 instead of 125 KB for the bounding box.
 constexpr int kRowBits = 1024;
 constexpr int kRowWords = 32;
-constexpr int kMaxChain = 4;          // frame pairs that share one source search
+constexpr int kMaxChain = 4;          // frame pairs that share one source search (forward members of a chain)
+constexpr int kMaxRev = 4;            // pairs answered from their TARGET side by one search (reverse members, k2_prep_kernel "cover")
+constexpr int kMaxMem = kMaxChain + kMaxRev;
 constexpr int kHashSize = 1024;       // target-cell hash (u32 entries) in shared memory
 constexpr int kHashMaxLoad = 640;     // candidates per search pass
 constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
@@ -38,7 +40,7 @@ constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entrie
 constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory
 constexpr int kFastCtasPerSm = 3;
 // sparse window (only the non-zero tile words + a presence/base table): 10 CTAs per SM
-constexpr int kSparseWords = 3936;    // non-zero tile words a sparse window can hold (15.4 KB)
+constexpr int kSparseWords = 3904;    // non-zero tile words a sparse window can hold (15.25 KB; with the tables, queues and control block 10 CTAs fill an SM at max_px = 500)
 constexpr int kSparseQCap = 144;
 constexpr int kSparseHash = 512;
 constexpr int kSparseHashMaxLoad = 320;
@@ -84,7 +86,35 @@ struct K2Params {
     int32_t* trace_len;          // [n_pairs] pixels on the path, 0 = None
     unsigned long long* err_key; // atomicMin: (item in reference order << 26 | target << 2 | code)
     long long orig_base;         // sources of the pairs that precede this call's pairs in the caller's batch (chunked host entry)
+    // cover (k2_prep_kernel): which sets are searched, and the pairs answered from their target side
+    const int* p1_prefix;        // [n_pairs+1] exclusive prefix of n_src over the chain leaders of SEARCHED sets: the tickets of the first pass
+    const int* rev_head;         // [n_pairs] head pair of a searched set -> its first reverse member, or -1
+    const int* rev_next;         // [n_pairs] next reverse member
+    const int* lead_of;          // [n_pairs] leader of the chain a pair belongs to (its directed work items)
+    uint32_t* item_bits;         // bitmap over the work items: already on the directed list
+    int* dir_list;               // work items that need their own (directed) search after all
+    const int32_t* comp_label;   // [n_masks][H][W] root pixel of the mask component, -1 off the mask (axb_components.cu); NULL: no cover
+    const int4* comp_ext;        // [n_masks][H * W] L1 extents of the component, at its root pixel
+    int reverse;                 // this launch attaches the reverse members (first pass and its dense list)
+    // where a fast kernel takes its work items from and where it puts the windows that do not fit
+    const int* src_list;         // NULL: tickets over p1_prefix
+    int src_len_ctr, src_ticket_ctr;
+    int* dense_out;
+    int dense_out_ctr;
 };
+
+// outputs of k2_prep_kernel (each [n_pairs + 1] ints)
+struct K2Prep {
+    int *work_prefix, *all_prefix, *next_same, *p1_prefix, *rev_head, *rev_next, *lead_of;
+    int *dst_head, *state;       // scratch of the cover decision
+    uint32_t* item_bits;         // [(total_src + 31) / 32]
+};
+constexpr int kPrepArrays = 9;
+
+// counters[]: [0] first-pass ticket, [1] general list length, [2] general ticket, [3] dense list A length, [4] its ticket,
+// [5] directed list length, [6] its ticket, [7] dense list B length, [8] its ticket
+enum { kCtrP1Ticket = 0, kCtrGenLen = 1, kCtrGenTicket = 2, kCtrDenseALen = 3, kCtrDenseATicket = 4, kCtrDirLen = 5,
+       kCtrDirTicket = 6, kCtrDenseBLen = 7, kCtrDenseBTicket = 8 };
 
 inline int k2_tile_rows(int max_px) { return (max_px + 3) / 4 + 1; }
 inline size_t k2_fast_smem_bytes(int max_px) {      // dense window + queues + hash
@@ -120,13 +150,13 @@ inline bool first_use_on_device(unsigned long long& flags) {
     return true;
 }
 
-void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
-                    int* next_same, int* counters, int n_masks, int n_dets, long long out_capacity, int total_src,
-                    unsigned long long* err_flags, cudaStream_t stream);
+void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, const K2Prep& o, int* counters, int n_masks, int n_dets,
+                    long long out_capacity, int total_src, int allow_reverse, unsigned long long* err_flags, cudaStream_t stream);
+void launch_k2_components(const uint32_t* mask_bits, int n_masks, int H, int W, int Wp, int* labels, int4* ext, cudaStream_t stream);
 void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint32_t* tiles, cudaStream_t stream);
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
-void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t stream);   // max_px 512 .. 1023: two passes
+void launch_k2_sparse_wide(const K2Params& p, int grid, bool second, cudaStream_t stream);   // max_px 512 .. 1023
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);     // max_px > kFastMaxPx: the wide kernel
 void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);

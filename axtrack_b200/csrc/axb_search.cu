@@ -497,15 +497,27 @@ __global__ void __launch_bounds__(256) k2_all_to_general_kernel(const int* __res
     if (blockIdx.x == 0 && threadIdx.x == 0) counters[1] = total;
 }
 
-// Chains + prefix sums + counter reset, one CTA.
+// Chains + cover + prefix sums + counter reset, one CTA.
 //   same key = same (mask_idx, src_off, n_src): the searches of the two pairs are identical, only
 //   the targets differ.  prev/next link same-key pairs inside a +-kChainWindow index window; a
 //   pair whose depth in its list is a multiple of kMaxChain leads a chain of <= kMaxChain pairs.
+//   The first pair of a list is the HEAD of its detection set.
+//
+// Cover (lim.allow_reverse).  A frame pair (t, t_bef) asks for the path lengths from the detections of t_bef to
+// those of t (AxonDetections.py:553-566).  On the mask the length does not depend on the direction (unit weights,
+// astar.cpp:122-136), so a search from a detection of t settles the pair as well as one from t_bef (what it cannot
+// settle falls back to a directed search, axb_components.cu).  The frames are the vertices and the pairs the edges
+// of a graph, and it is enough to search from a vertex cover: with pairs at distance 1 and 2 two frames of three.
+// Greedy, in the order of the heads: a set that no earlier decision forces to be searched and whose pairs all
+// lead to searchable sets with room in their chains is NOT searched; its pairs become REVERSE members of the
+// chains of their target sets (rev_head / rev_next), which are thereby forced to be searched.
 constexpr int kChainWindow = 16;
+constexpr int kPrepSmemPairs = 4096;            // cover decided in shared memory up to this many pairs (else in global memory)
 struct PrepLimits {
     int n_masks, n_dets;            // mask_idx in [0, n_masks), detection rows in [0, n_dets]
     long long out_capacity;         // out_off + n_src * n_dst <= out_capacity
     int total_src;                  // capacity of the deferred-work lists (sum of n_src the caller sized them for)
+    int allow_reverse;
 };
 __device__ __forceinline__ bool pair_ok(const axb_pair_desc& a, const PrepLimits& lim) {
     return a.n_src >= 0 && a.n_dst >= 0 && a.src_off >= 0 && a.dst_off >= 0 &&
@@ -515,17 +527,22 @@ __device__ __forceinline__ bool pair_ok(const axb_pair_desc& a, const PrepLimits
 }
 // A descriptor that points outside the caller's buffers gets no work (and status flag 32): the search
 // kernels never see it.  Same when the pairs hold more sources than the work lists were sized for.
-__global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __restrict__ pairs, int n_pairs,
-                                                         int* __restrict__ work_prefix, int* __restrict__ all_prefix,
-                                                         int* __restrict__ next_same, int* __restrict__ counters,
-                                                         const PrepLimits lim, unsigned long long* __restrict__ err_flags) {
-    __shared__ int s_carry[2];
-    __shared__ int s_warp[2][32];
+__global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __restrict__ pairs, int n_pairs, K2Prep o,
+                                                         int* __restrict__ counters, const PrepLimits lim,
+                                                         unsigned long long* __restrict__ err_flags) {
+    extern __shared__ int s_dyn[];
+    __shared__ int s_carry[3];
+    __shared__ int s_warp[3][32];
     __shared__ int s_bad;
     const int tid = threadIdx.x;
+    int* const work_prefix = o.work_prefix;
+    int* const all_prefix = o.all_prefix;
+    int* const next_same = o.next_same;
     int* const prev = work_prefix;            // scratch until the scan overwrites it
-    if (tid < 8) counters[tid] = 0;
+    int* const head_of = o.p1_prefix;         // scratch until the scan overwrites it: head pair of the pair's source set
+    if (tid < 16) counters[tid] = 0;
     if (tid == 0) s_bad = 0;
+    for (int i = tid; i < (lim.total_src + 31) / 32; i += blockDim.x) o.item_bits[i] = 0u;
     __syncthreads();
     for (int i = tid; i < n_pairs; i += blockDim.x) {
         const axb_pair_desc a = pairs[i];
@@ -544,61 +561,133 @@ __global__ void __launch_bounds__(1024) k2_prep_kernel(const axb_pair_desc* __re
         }
         prev[i] = pv;
         next_same[i] = nx;
+        o.rev_head[i] = -1;
+        o.rev_next[i] = -1;
+        o.state[i] = (ok && a.n_src > 0) ? 0 : -1;          // -1: no work; else bits 0-1 = 1 searched / 2 not searched, bit 2 forced, bits 4.. reverse members
     }
     __syncthreads();
-    // depth in the list -> leader flag, kept in all_prefix until the scan
+    // depth in the list -> leader flag (kept in all_prefix until the scan), head of the set, leader of the pair's chain
     for (int i = tid; i < n_pairs; i += blockDim.x) {
-        int d = 0;
-        for (int q = prev[i]; q >= 0; q = prev[q]) ++d;
+        int d = 0, h = i;
+        for (int q = prev[i]; q >= 0; q = prev[q]) { ++d; h = q; }
         all_prefix[i] = (d % kMaxChain) == 0;
+        head_of[i] = o.state[i] < 0 ? -1 : h;
+        int l = i;
+        for (int k = d % kMaxChain; k > 0; --k) l = prev[l];
+        o.lead_of[i] = l;
     }
     __syncthreads();
-    if (tid == 0) { s_carry[0] = 0; s_carry[1] = 0; }
+    // head of the set a pair's TARGETS are (-1: that set is never a source, it cannot be searched; -2: no targets)
+    for (int i = tid; i < n_pairs; i += blockDim.x) {
+        int dh = -1;
+        if (o.state[i] >= 0) {
+            const axb_pair_desc a = pairs[i];
+            if (a.n_dst == 0) dh = -2;
+            else {
+                for (int q = max(0, i - kChainWindow); q <= min(n_pairs - 1, i + kChainWindow); ++q) {
+                    const axb_pair_desc b = pairs[q];
+                    if (o.state[q] >= 0 && b.mask_idx == a.mask_idx && b.src_off == a.dst_off && b.n_src == a.n_dst) { dh = head_of[q]; break; }
+                }
+            }
+        }
+        o.dst_head[i] = dh;
+    }
+    __syncthreads();
+    {   // the cover: sequential over the heads, on shared-memory copies when they fit
+        const bool in_smem = n_pairs <= kPrepSmemPairs;
+        int* const nxt = in_smem ? s_dyn : next_same;
+        int* const dsh = in_smem ? s_dyn + n_pairs : o.dst_head;
+        int* const st = in_smem ? s_dyn + 2 * n_pairs : o.state;
+        int* const rh = in_smem ? s_dyn + 3 * n_pairs : o.rev_head;
+        int* const rn = in_smem ? s_dyn + 4 * n_pairs : o.rev_next;
+        if (in_smem) {
+            for (int i = tid; i < n_pairs; i += blockDim.x) { nxt[i] = next_same[i]; dsh[i] = o.dst_head[i]; st[i] = o.state[i]; rh[i] = -1; rn[i] = -1; }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            for (int h = 0; h < n_pairs; ++h) {
+                if (st[h] < 0 || head_of[h] != h) continue;
+                bool skip = lim.allow_reverse && !(st[h] & 4);
+                int len = 0;
+                for (int q = h; q >= 0 && skip; q = nxt[q]) ++len;
+                for (int q = h; q >= 0 && skip; q = nxt[q]) {
+                    const int D = dsh[q];
+                    if (D == -2) continue;
+                    if (D < 0 || D == h || (st[D] & 3) == 2 || (st[D] >> 4) + len > kMaxRev) skip = false;
+                }
+                if (!skip) { st[h] = (st[h] & ~3) | 1; continue; }
+                st[h] = (st[h] & ~3) | 2;
+                for (int q = h; q >= 0; q = nxt[q]) {
+                    const int D = dsh[q];
+                    if (D == -2) continue;
+                    st[D] = (st[D] | 4) + 16;
+                    rn[q] = rh[D];
+                    rh[D] = q;
+                }
+            }
+        }
+        __syncthreads();
+        if (in_smem) {
+            for (int i = tid; i < n_pairs; i += blockDim.x) { o.state[i] = st[i]; o.rev_head[i] = rh[i]; o.rev_next[i] = rn[i]; }
+            __syncthreads();
+        }
+    }
+    // searched flag of every pair (by its source set), kept in dst_head until the scan is done
+    for (int i = tid; i < n_pairs; i += blockDim.x) o.dst_head[i] = (o.state[i] >= 0 && (o.state[head_of[i]] & 3) == 1) ? 1 : 0;
+    __syncthreads();
+    if (tid == 0) { s_carry[0] = 0; s_carry[1] = 0; s_carry[2] = 0; }
     __syncthreads();
     for (int base = 0; base < n_pairs; base += blockDim.x) {
         const int i = base + tid;
         int na = 0;
         if (i < n_pairs) { const axb_pair_desc a = pairs[i]; na = pair_ok(a, lim) ? a.n_src : 0; }
         const int nw = (i < n_pairs && all_prefix[i]) ? na : 0;
-        int xa = na, xw = nw;
-        for (int o = 1; o < 32; o <<= 1) {
-            const int ya = __shfl_up_sync(kFull, xa, o), yw = __shfl_up_sync(kFull, xw, o);
-            if ((tid & 31) >= o) { xa += ya; xw += yw; }
+        const int np = (i < n_pairs && o.dst_head[i]) ? nw : 0;
+        int xa = na, xw = nw, xp = np;
+        for (int k = 1; k < 32; k <<= 1) {
+            const int ya = __shfl_up_sync(kFull, xa, k), yw = __shfl_up_sync(kFull, xw, k), yp = __shfl_up_sync(kFull, xp, k);
+            if ((tid & 31) >= k) { xa += ya; xw += yw; xp += yp; }
         }
-        if ((tid & 31) == 31) { s_warp[0][tid >> 5] = xa; s_warp[1][tid >> 5] = xw; }
+        if ((tid & 31) == 31) { s_warp[0][tid >> 5] = xa; s_warp[1][tid >> 5] = xw; s_warp[2][tid >> 5] = xp; }
         __syncthreads();
         if (tid < 32) {
             int wa = tid < (int)(blockDim.x >> 5) ? s_warp[0][tid] : 0;
             int ww = tid < (int)(blockDim.x >> 5) ? s_warp[1][tid] : 0;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int ya = __shfl_up_sync(kFull, wa, o), yw = __shfl_up_sync(kFull, ww, o);
-                if (tid >= o) { wa += ya; ww += yw; }
+            int wp = tid < (int)(blockDim.x >> 5) ? s_warp[2][tid] : 0;
+            for (int k = 1; k < 32; k <<= 1) {
+                const int ya = __shfl_up_sync(kFull, wa, k), yw = __shfl_up_sync(kFull, ww, k), yp = __shfl_up_sync(kFull, wp, k);
+                if (tid >= k) { wa += ya; ww += yw; wp += yp; }
             }
-            s_warp[0][tid] = wa; s_warp[1][tid] = ww;
+            s_warp[0][tid] = wa; s_warp[1][tid] = ww; s_warp[2][tid] = wp;
         }
         __syncthreads();
         const int offa = (tid >> 5) ? s_warp[0][(tid >> 5) - 1] : 0;
         const int offw = (tid >> 5) ? s_warp[1][(tid >> 5) - 1] : 0;
-        const int incla = s_carry[0] + offa + xa, inclw = s_carry[1] + offw + xw;
+        const int offp = (tid >> 5) ? s_warp[2][(tid >> 5) - 1] : 0;
+        const int incla = s_carry[0] + offa + xa, inclw = s_carry[1] + offw + xw, inclp = s_carry[2] + offp + xp;
         __syncthreads();
-        if (i < n_pairs) { all_prefix[i] = incla - na; work_prefix[i] = inclw - nw; }
-        if (tid == (int)blockDim.x - 1) { s_carry[0] = incla; s_carry[1] = inclw; }
+        if (i < n_pairs) { all_prefix[i] = incla - na; work_prefix[i] = inclw - nw; o.p1_prefix[i] = inclp - np; }
+        if (tid == (int)blockDim.x - 1) { s_carry[0] = incla; s_carry[1] = inclw; s_carry[2] = inclp; }
         __syncthreads();
     }
     if (tid == 0) {
         const bool over = s_carry[1] > lim.total_src;        // the deferred-work lists would overflow: no work at all
         all_prefix[n_pairs] = s_carry[0];
         work_prefix[n_pairs] = over ? 0 : s_carry[1];
+        o.p1_prefix[n_pairs] = over ? 0 : s_carry[2];
         if (s_bad || over) atomicOr(err_flags, 32ull);
     }
 }
 
-void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, int* work_prefix, int* all_prefix,
-                    int* next_same, int* counters, int n_masks, int n_dets, long long out_capacity, int total_src,
-                    unsigned long long* err_flags, cudaStream_t stream) {
+void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, const K2Prep& o, int* counters, int n_masks, int n_dets,
+                    long long out_capacity, int total_src, int allow_reverse, unsigned long long* err_flags, cudaStream_t stream) {
+    static unsigned long long attr_set = 0ull;
+    if (first_use_on_device(attr_set))
+        cudaFuncSetAttribute(k2_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * kPrepSmemPairs * (int)sizeof(int));
     PrepLimits lim;
-    lim.n_masks = n_masks; lim.n_dets = n_dets; lim.out_capacity = out_capacity; lim.total_src = total_src;
-    k2_prep_kernel<<<1, 1024, 0, stream>>>(pairs, n_pairs, work_prefix, all_prefix, next_same, counters, lim, err_flags);
+    lim.n_masks = n_masks; lim.n_dets = n_dets; lim.out_capacity = out_capacity; lim.total_src = total_src; lim.allow_reverse = allow_reverse;
+    const size_t smem = n_pairs <= kPrepSmemPairs ? 5 * (size_t)n_pairs * sizeof(int) : 0;
+    k2_prep_kernel<<<1, 1024, smem, stream>>>(pairs, n_pairs, o, counters, lim, err_flags);
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {

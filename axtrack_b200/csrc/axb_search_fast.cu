@@ -125,17 +125,37 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
         while (q >= 0 && nm < kMaxChain) {
             const axb_pair_desc pd = p.pairs[q];
             ch.orow[nm] = pd.out_off + (long long)si * pd.n_dst;
-            ch.item_orig[nm] = p.orig_base + (long long)p.all_prefix[q] + si;
+            ch.ostride[nm] = 1;
+            ch.ebase[nm] = p.all_prefix[q];
             ch.dst_off[nm] = pd.dst_off;
+            ch.ditem[nm] = 0;
             ch.cum[nm + 1] = ch.cum[nm] + max(pd.n_dst, 0);
             ++nm;
             q = p.next_same[q];
         }
+        uint32_t rm = 0u;
+        if (p.reverse) {               // pairs this detection is a target of and whose sources are not searched
+            for (q = p.rev_head[lo]; q >= 0 && nm < kMaxMem; q = p.rev_next[q]) {
+                const axb_pair_desc pd = p.pairs[q];
+                ch.orow[nm] = pd.out_off + si;
+                ch.ostride[nm] = pd.n_dst;
+                ch.ebase[nm] = p.all_prefix[q];
+                ch.dst_off[nm] = pd.src_off;
+                ch.ditem[nm] = p.work_prefix[p.lead_of[q]];
+                ch.cum[nm + 1] = ch.cum[nm] + max(pd.n_src, 0);
+                rm |= 1u << nm;
+                ++nm;
+            }
+        }
         ch.nm = nm;
+        ch.si = si;
+        ch.revmask = rm;
+        ch.mask_idx = lead.mask_idx;
     }
     __syncthreads();
     const int nm = ch.nm;
     const int total_t = ch.cum[nm];
+    const uint32_t revmask = ch.revmask;
     if (total_t <= 0) return kItemDone;
 
     const int sy = p.dets_yx[2 * ((size_t)lead.src_off + si)];
@@ -146,38 +166,62 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
     w.oy = sy & 3; w.ox = sx & 31;                         // only used when the source is in the grid
     w.ty0 = sy >> 2; w.tx0 = (sx >> 5) * 4;
     const bool src_in = sy >= 0 && sy < p.H && sx >= 0 && sx < p.W;
+    const bool src_on = src_in && ((__ldg(p.mask_bits + ((size_t)lead.mask_idx * p.H + sy) * p.Wp + (sx >> 5)) >> (sx & 31)) & 1u);
     const long long r2 = (long long)RW * RW;
     constexpr int kPassLoad = C::kMaxLoad > NT ? C::kMaxLoad - NT : 0;
 
     int tt = 0;                        // next target of the flattened chain target list
+    bool to_gen = false;
     for (;;) {                         // passes of <= kMaxLoad candidates (one on real data)
         for (int i = tid; i < HASH; i += NT) hash[i] = kEmpty;
-        if (tid == 0) { ctl.ncand = 0; ctl.alloc = 0; }
+        if (tid == 0) { ctl.ncand = 0; ctl.alloc = 0; ctl.nchk = 0; }
         for (;;) {                     // groups of NT targets
             __syncthreads();
             if (tt >= total_t || ctl.ncand > kPassLoad) break;
             const int t = tt + tid;
-            bool is_cand = false, self = false;
+            bool is_cand = false, self = false, chk = false;
             int m = 0, j = 0, dy = 0, dx = 0;
             if (t < total_t) {
                 while (m + 1 < nm && t >= ch.cum[m + 1]) ++m;
                 j = t - ch.cum[m];
+                const bool rev = (revmask >> m) & 1u;
                 const int ty = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j)];
                 const int tx = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j) + 1];
                 dy = ty - sy; dx = tx - sx;
                 const long long d2 = (long long)dy * dy + (long long)dx * dx;
                 if (d2 < r2) {                                        // AxonDetections.py:620-623
                     const bool t_in = ty >= 0 && ty < p.H && tx >= 0 && tx < p.W;
-                    const unsigned long long ek = ((unsigned long long)ch.item_orig[m] << 26) | ((unsigned long long)j << 2);
-                    if (!src_in) atomicMin(p.err_key, ek | 1ull);     // astar_wrapper.py:39-42
-                    else if (!t_in) atomicMin(p.err_key, ek | 2ull);  // astar_wrapper.py:43-45
+                    // the reference's start is this detection (forward) or the other one (reverse member)
+                    const bool start_in = rev ? t_in : src_in, goal_in = rev ? src_in : t_in;
+                    const unsigned long long ek = rev ? (((unsigned long long)(p.orig_base + ch.ebase[m] + j) << 26) | ((unsigned long long)si << 2))
+                                                      : (((unsigned long long)(p.orig_base + ch.ebase[m] + si) << 26) | ((unsigned long long)j << 2));
+                    if (!start_in) atomicMin(p.err_key, ek | 1ull);    // astar_wrapper.py:39-42
+                    else if (!goal_in) atomicMin(p.err_key, ek | 2ull);  // astar_wrapper.py:43-45
                     else if (dy == 0 && dx == 0) self = true;         // start == goal: L = 1 (astar.cpp:67,99)
                     else is_cand = abs(dy) + abs(dx) < RW;            // farther cells need > max_px pixels
+                    // reverse member: "not reached from here" is the reference's None only if the other detection's own
+                    // level 0 is known to reach hop max_px (axb_components.cu); else it gets its own search afterwards
+                    if (rev && is_cand) {
+                        chk = !component_reaches(p, ch.mask_idx, ty, tx, RW);
+                        if (!src_on) {             // a path INTO an off-mask cell is not a level-0 path: nothing to settle from here
+                            is_cand = false;
+                            if (chk) {
+                                const int it = ch.ditem[m] + j;
+                                const uint32_t bit = 1u << (it & 31);
+                                if (!(atomicOr(&p.item_bits[it >> 5], bit) & bit)) p.dir_list[atomicAdd(&p.counters[kCtrDirLen], 1)] = it;
+                                chk = false;
+                            }
+                        }
+                    }
                 }
-                const long long oo = ch.orow[m] + j;
+                const long long oo = ch.orow[m] + (long long)j * ch.ostride[m];
                 p.path_len[oo] = self ? 1 : RW;                       // None -> max_px (AxonDetections.py:736)
                 p.unreachable[oo] = self ? 0 : 1;
                 if (p.wcost) p.wcost[oo] = self ? 0.f : __int_as_float(0x7f800000);
+            }
+            if (revmask) {
+                const uint32_t cb = __ballot_sync(kFull, chk);
+                if (cb && lane == 0) atomicAdd(&ctl.nchk, __popc(cb));
             }
             const uint32_t bal = __ballot_sync(kFull, is_cand);
             if (bal) {
@@ -187,7 +231,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 if (is_cand) {
                     const uint32_t slot = (uint32_t)base + __popc(bal & lt);
                     AXB_ASSERT(slot < (uint32_t)kCandCap && slot < 2048u);
-                    cand[slot] = ((uint32_t)m << 30) | (uint32_t)j;
+                    cand[slot] = ((uint32_t)m << 29) | (chk ? 1u << 28 : 0u) | (uint32_t)j;
                     int bit;
                     const uint32_t key = cell_key<LOGC>(dy, dx, w.oy, w.ox, NR, bit);
                     AXB_ASSERT(((key & G::WMASK) >> LOGC) < (uint32_t)NR && bit >= 0 && bit < 32 && slot < (1u << G::SLOTB));
@@ -382,32 +426,72 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
 #endif
             }
             AXB_T(2, tclk); AXB_C(4, 1);
-            if (defer || (!hit && unsettled > 0)) return kItemToGeneral;   // level 0 cannot answer
+            if (revmask && (defer || ctl.nchk > 0)) {
+                // reverse members: what this search did not reach stays None only where that is certain (nothing is
+                // certain after a frontier overflow); the others get their own directed search in a later launch
+                for (int i = tid; i < ncand; i += NT) {
+                    const uint32_t c = cand[i];
+                    const int m = (int)(c >> 29);
+                    if (!((revmask >> m) & 1u) || !(defer || ((c >> 28) & 1u))) continue;
+                    const int jj = (int)(c & 0x0FFFFFFFu);
+                    const long long oo = ch.orow[m] + (long long)jj * ch.ostride[m];
+                    if (*(volatile const uint8_t*)(p.unreachable + oo)) {
+                        const int it = ch.ditem[m] + jj;
+                        const uint32_t bit = 1u << (it & 31);
+                        if (!(atomicOr(&p.item_bits[it >> 5], bit) & bit)) p.dir_list[atomicAdd(&p.counters[kCtrDirLen], 1)] = it;
+                    }
+                }
+            }
+            if (defer || (!hit && unsettled > 0)) {                   // level 0 cannot answer the forward members
+                if (!revmask) return kItemToGeneral;
+                to_gen = true;                                        // the reverse members of later passes are still due
+            }
         }
         if (tt >= total_t) break;
     }
-    return kItemDone;
+    return to_gen ? kItemToGeneral : kItemDone;
 }
 
 }  // namespace
 
-// Persistent CTAs over a ticket counter.  The sparse kernel sees every work item first.
+// Next work item of this launch (-1: none left).  First pass: tickets over the sources of the SEARCHED sets
+// (p1_prefix); later passes: a list a previous launch wrote.
+__device__ __forceinline__ int fetch_item(const K2Params& p, Ctl& ctl) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int t = atomicAdd(&p.counters[p.src_ticket_ctr], 1);
+        int item = -1;
+        if (p.src_list) {
+            if (t < p.counters[p.src_len_ctr]) item = p.src_list[t];
+        } else if (t < p.p1_prefix[p.n_pairs]) {
+            int lo = 0, hi = p.n_pairs - 1;
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (p.p1_prefix[mid] <= t) lo = mid; else hi = mid - 1;
+            }
+            item = p.work_prefix[lo] + (t - p.p1_prefix[lo]);
+        }
+        ctl.item = item;
+    }
+    __syncthreads();
+    return ctl.item;
+}
+
+__device__ __forceinline__ void defer_item(const K2Params& p, int r, int item) {
+    if (threadIdx.x != 0) return;
+    if (r == kItemToGeneral) p.gen_list[atomicAdd(&p.counters[kCtrGenLen], 1)] = item;
+    else if (r == kItemToDense) p.dense_out[atomicAdd(&p.counters[p.dense_out_ctr], 1)] = item;
+}
+
+// Persistent CTAs over a ticket counter.
 __global__ void __launch_bounds__(kFastThreads, kSparseCtasPerSm) k2_sparse_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
-    const int total = p.work_prefix[p.n_pairs];
     for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[0], 1);
-        __syncthreads();
-        const int item = ctl.item;
-        if (item >= total) break;
-        const int r = run_item_fast<true>(p, item, smem, gscr, ctl);
-        if (threadIdx.x == 0) {
-            if (r == kItemToGeneral) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
-            else if (r == kItemToDense) p.dense_list[atomicAdd(&p.counters[3], 1)] = item;
-        }
+        const int item = fetch_item(p, ctl);
+        if (item < 0) break;
+        defer_item(p, run_item_fast<true>(p, item, smem, gscr, ctl), item);
     }
 }
 
@@ -416,47 +500,34 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k2_fast_kernel(c
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
-    const int total = p.counters[3];
     for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[4], 1);
-        __syncthreads();
-        const int t = ctl.item;
-        if (t >= total) break;
-        const int item = p.dense_list[t];
-        const int r = run_item_fast<false>(p, item, smem, gscr, ctl);
-        if (r == kItemToGeneral && threadIdx.x == 0) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
+        const int item = fetch_item(p, ctl);
+        if (item < 0) break;
+        defer_item(p, run_item_fast<false>(p, item, smem, gscr, ctl), item);
     }
 }
 
 // max_px 512 .. 1023: the same sparse-window search on the 256-column circle (257 folded rows, 18-bit word keys).
 // Windows with more non-zero tile words than the layout holds, and everything level 0 cannot answer, go to the
 // all-levels kernel (k2_general_wide_kernel).
-// First pass (SECOND = false): every work item, windows of up to kWideWords non-zero tile words, 2 CTAs per SM; items
-// whose window holds more go to the dense list.  Second pass (SECOND = true): those items with windows of up to
-// kWideWords2 words, 1 CTA per SM.  What neither holds (e.g. an all-ones mask: 65 792 words) goes to the all-levels kernel.
+// First kind (SECOND = false): windows of up to kWideWords non-zero tile words, 2 CTAs per SM; items whose window holds
+// more go to a dense list.  Second kind (SECOND = true): those items with windows of as many words as one CTA per SM
+// can hold.  What neither holds (e.g. an all-ones mask: 65 792 words) goes to the all-levels kernel.
 template <bool SECOND>
 __global__ void __launch_bounds__(32 * kWideNW, SECOND ? 1 : kWideSparseCtasPerSm) k2_sparse_wide_kernel(const K2Params p) {
     extern __shared__ __align__(16) uint32_t smem[];
     __shared__ Ctl ctl;
     uint32_t* const gscr = p.fast_scratch + (size_t)blockIdx.x * kFastScratchWords;
-    const int total = SECOND ? p.counters[3] : p.work_prefix[p.n_pairs];
     for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[SECOND ? 4 : 0], 1);
-        __syncthreads();
-        const int t = ctl.item;
-        if (t >= total) break;
-        const int item = SECOND ? p.dense_list[t] : t;
-        const int r = run_item_fast<true, 8, kWideNW>(p, item, smem, gscr, ctl);
-        if (threadIdx.x == 0) {
-            if (r == kItemToGeneral || (SECOND && r == kItemToDense)) p.gen_list[atomicAdd(&p.counters[1], 1)] = item;
-            else if (r == kItemToDense) p.dense_list[atomicAdd(&p.counters[3], 1)] = item;
-        }
+        const int item = fetch_item(p, ctl);
+        if (item < 0) break;
+        int r = run_item_fast<true, 8, kWideNW>(p, item, smem, gscr, ctl);
+        if (SECOND && r == kItemToDense) r = kItemToGeneral;
+        defer_item(p, r, item);
     }
 }
 
-void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t stream) {
+void launch_k2_sparse_wide(const K2Params& p, int grid, bool second, cudaStream_t stream) {
     static unsigned long long attr_set = 0ull;
     const size_t fixed = k2_sparse_wide_smem_bytes(p.max_px) - (size_t)kWideWords * sizeof(uint32_t);
     if (first_use_on_device(attr_set)) {
@@ -467,12 +538,14 @@ void launch_k2_sparse_wide(const K2Params& p, int grid, int grid2, cudaStream_t 
     }
     K2Params q = p;
     q.hash_smem = 1;               // two CTAs per SM leave room for the target hash in shared memory (the probe is on the wave's critical path)
-    q.sparse_words = kWideWords;
     const size_t hash_bytes = kWideHash * sizeof(uint32_t);
-    k2_sparse_wide_kernel<false><<<grid, 32 * kWideNW, k2_sparse_wide_smem_bytes(p.max_px) + hash_bytes, stream>>>(q);
-    // second pass: as many words as one CTA per SM can hold next to the tables, queues and hash
-    q.sparse_words = (int)(((size_t)226 * 1024 - fixed - hash_bytes) / sizeof(uint32_t)) & ~3;
-    k2_sparse_wide_kernel<true><<<grid2, 32 * kWideNW, fixed + hash_bytes + (size_t)q.sparse_words * sizeof(uint32_t), stream>>>(q);
+    if (!second) {
+        q.sparse_words = kWideWords;
+        k2_sparse_wide_kernel<false><<<grid, 32 * kWideNW, k2_sparse_wide_smem_bytes(p.max_px) + hash_bytes, stream>>>(q);
+    } else {                       // as many words as one CTA per SM can hold next to the tables, queues and hash
+        q.sparse_words = (int)(((size_t)226 * 1024 - fixed - hash_bytes) / sizeof(uint32_t)) & ~3;
+        k2_sparse_wide_kernel<true><<<grid, 32 * kWideNW, fixed + hash_bytes + (size_t)q.sparse_words * sizeof(uint32_t), stream>>>(q);
+    }
 }
 
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {

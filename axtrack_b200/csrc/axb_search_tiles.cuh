@@ -62,12 +62,20 @@ template <> __device__ __forceinline__ uint32_t hash_slot<1024>(uint32_t key) { 
 template <> __device__ __forceinline__ uint32_t hash_slot<512>(uint32_t key) { return (key * 0x9E3779B1u) >> 23; }
 static_assert(kCandCap <= 2048 && kSparseHashMaxLoad <= 512, "hash entries keep 11 (wide layout: 9) bits of candidate slot");
 
+// Members of a chain: forward pairs (this source's row of the pair's matrix, targets = the pair's dst detections)
+// and reverse pairs (k2_prep_kernel "cover": this detection is a TARGET of the pair; the search answers its column,
+// the flattened "targets" of the member are the pair's SOURCE detections).
 struct Chain {
-    long long orow[kMaxChain];      // first output element of this source's row, per member pair
-    long long item_orig[kMaxChain]; // work index in the reference's iteration order (errors)
-    int dst_off[kMaxChain];
-    int cum[kMaxChain + 1];         // flattened target index space
+    long long orow[kMaxMem];        // output element of flattened target 0 of the member ...
+    int ebase[kMaxMem];             // first work index of the pair in the reference's iteration order (errors; + K2Params::orig_base)
+    int ostride[kMaxMem];           // ... and the step to the next one: 1 (forward: along the row) or n_dst (reverse: down the column)
+    int dst_off[kMaxMem];           // detections the flattened targets are
+    int ditem[kMaxMem];             // reverse: work item of flattened target 0 (its own directed search, if it comes to that)
+    int cum[kMaxMem + 1];           // flattened target index space
     int nm;
+    int si;                         // index of this detection in its set
+    uint32_t revmask;               // bit m: member m is a reverse member
+    int mask_idx;
 };
 
 struct __align__(16) Ctl {
@@ -78,6 +86,7 @@ struct __align__(16) Ctl {
     int ncand;
     int item;
     int alloc;         // sparse: packed tile words allocated so far
+    int nchk;          // reverse candidates whose None needs the directed search unless this search settles them
 };
 
 struct Win {
@@ -200,6 +209,16 @@ __device__ __forceinline__ void sts64_if(uint32_t a, uint32_t x, uint32_t y, uin
                  :: "r"(a), "r"(x), "r"(y), "r"(want) : "memory");
 }
 
+// Does the mask component of pixel (y, x) hold a pixel at L1 distance >= RW from it?  Then the level-0 wavefront of
+// a search from (y, x) reaches hop RW (axb_components.cu) and every target it does not settle is None.
+__device__ __forceinline__ bool component_reaches(const K2Params& p, int mask_idx, int y, int x, int RW) {
+    const size_t base = (size_t)mask_idx * p.H * p.W;
+    const int r = __ldg(p.comp_label + base + (size_t)y * p.W + x);
+    if (r < 0) return false;
+    const int4 e = __ldg(p.comp_ext + base + r);
+    return max(max(e.x - (y + x), e.y - (y - x)), max(e.z - (x - y), e.w + (y + x))) >= RW;
+}
+
 // Slow path of the target probe: the hash slot of tile word `key` is occupied.  The cells
 // `claimed` of the word were reached with j mask pixels on the path (hop j, path length j+1).
 template <int HASH, int LOGC = 7>
@@ -213,7 +232,7 @@ __device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash
         if (e == kEmpty) break;
         if ((e >> G::ESH) == key && ((claimed >> ((e >> G::SLOTB) & 31u)) & 1u)) {
             const uint32_t c = cand[e & ((1u << G::SLOTB) - 1u)];
-            const long long o = ch.orow[c >> 30] + (long long)(c & 0x3FFFFFFFu);
+            const long long o = ch.orow[c >> 29] + (long long)(c & 0x0FFFFFFFu) * ch.ostride[c >> 29];
             p.path_len[o] = j + 1;
             p.unreachable[o] = 0;
             if (p.wcost) p.wcost[o] = (float)j;
