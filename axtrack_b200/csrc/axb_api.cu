@@ -337,7 +337,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
             int h[16];
             cudaStreamSynchronize(s);
             cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
-            fprintf(stderr, "[axb] wide K2: %d sources, %d searched in the first pass, %d to the second kind, %d directed, %d to the all-levels kernel\n",
+            fprintf(stderr, "[axb] wide K2: %d sources, %d first-pass tickets, %d to the second kind, %d directed, %d to the all-levels kernel\n",
                     total_src, h[0], h[3], h[5], h[1]);
         }
         return AXB_OK;
@@ -367,7 +367,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
         int h[16];
         cudaStreamSynchronize(s);
         cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
-        fprintf(stderr, "[axb] K2: %d sources, %d searched in the first pass, %d dense windows, %d directed (+%d dense), %d to the all-levels kernel\n",
+        fprintf(stderr, "[axb] K2: %d sources, %d first-pass tickets, %d dense windows, %d directed (+%d dense), %d to the all-levels kernel\n",
                 total_src, h[0], h[3], h[5], h[7], h[1]);
     }
     return AXB_OK;

@@ -202,15 +202,14 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     // reverse member: "not reached from here" is the reference's None only if the other detection's own
                     // level 0 is known to reach hop max_px (axb_components.cu); else it gets its own search afterwards
                     if (rev && is_cand) {
-                        chk = !component_reaches(p, ch.mask_idx, ty, tx, RW);
-                        if (!src_on) {             // a path INTO an off-mask cell is not a level-0 path: nothing to settle from here
+                        const int reach = component_reaches(p, ch.mask_idx, ty, tx, RW);
+                        chk = reach <= 0;
+                        // nothing to settle from here when the other detection is off the mask (it is no open cell of
+                        // this window) or this one is (a path INTO an off-mask cell is not a level-0 path)
+                        if (reach < 0 || !src_on) {
                             is_cand = false;
-                            if (chk) {
-                                const int it = ch.ditem[m] + j;
-                                const uint32_t bit = 1u << (it & 31);
-                                if (!(atomicOr(&p.item_bits[it >> 5], bit) & bit)) p.dir_list[atomicAdd(&p.counters[kCtrDirLen], 1)] = it;
-                                chk = false;
-                            }
+                            if (chk) push_directed(p, ch.ditem[m] + j, reach < 0);
+                            chk = false;
                         }
                     }
                 }
@@ -436,9 +435,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     const int jj = (int)(c & 0x0FFFFFFFu);
                     const long long oo = ch.orow[m] + (long long)jj * ch.ostride[m];
                     if (*(volatile const uint8_t*)(p.unreachable + oo)) {
-                        const int it = ch.ditem[m] + jj;
-                        const uint32_t bit = 1u << (it & 31);
-                        if (!(atomicOr(&p.item_bits[it >> 5], bit) & bit)) p.dir_list[atomicAdd(&p.counters[kCtrDirLen], 1)] = it;
+                        push_directed(p, ch.ditem[m] + jj, false);
                     }
                 }
             }

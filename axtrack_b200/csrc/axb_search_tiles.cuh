@@ -211,12 +211,23 @@ __device__ __forceinline__ void sts64_if(uint32_t a, uint32_t x, uint32_t y, uin
 
 // Does the mask component of pixel (y, x) hold a pixel at L1 distance >= RW from it?  Then the level-0 wavefront of
 // a search from (y, x) reaches hop RW (axb_components.cu) and every target it does not settle is None.
-__device__ __forceinline__ bool component_reaches(const K2Params& p, int mask_idx, int y, int x, int RW) {
+// 1: yes, 0: no, -1: (y, x) is off the mask.
+__device__ __forceinline__ int component_reaches(const K2Params& p, int mask_idx, int y, int x, int RW) {
     const size_t base = (size_t)mask_idx * p.H * p.W;
     const int r = __ldg(p.comp_label + base + (size_t)y * p.W + x);
-    if (r < 0) return false;
+    if (r < 0) return -1;
     const int4 e = __ldg(p.comp_ext + base + r);
-    return max(max(e.x - (y + x), e.y - (y - x)), max(e.z - (x - y), e.w + (y + x))) >= RW;
+    return max(max(e.x - (y + x), e.y - (y - x)), max(e.z - (x - y), e.w + (y + x))) >= RW ? 1 : 0;
+}
+
+// A detection of a set that is not searched needs its own search after all: once per work item.  On the mask: the
+// level-0 kernels again (directed list); off the mask its level 0 is at most its four neighbours, so straight to
+// the all-levels kernel.
+__device__ __forceinline__ void push_directed(const K2Params& p, int item, bool off_mask) {
+    const uint32_t bit = 1u << (item & 31);
+    if (atomicOr(&p.item_bits[item >> 5], bit) & bit) return;
+    if (off_mask) p.gen_list[atomicAdd(&p.counters[kCtrGenLen], 1)] = item;
+    else p.dir_list[atomicAdd(&p.counters[kCtrDirLen], 1)] = item;
 }
 
 // Slow path of the target probe: the hash slot of tile word `key` is occupied.  The cells

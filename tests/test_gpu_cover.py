@@ -1,0 +1,176 @@
+"""K2 cover (axb_search.cu k2_prep_kernel, axb_components.cu): frame pairs answered from their TARGET side.
+Every case is compared pair by pair with the oracle (the closed form pinned to the compiled reference in
+tests/test_oracle_golden.py), bit-exact.  The masks are chosen to stress what the cover relies on:
+components smaller and larger than max_px, detections off the mask on either side, empty frames, chains of
+three pairs, errors raised inside reverse pairs, the 256-column kernels."""
+import numpy as np
+import pytest
+
+import oracle
+from axtrack_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail('-m gpu tests need a CUDA device (no CPU fallback exists)')
+    torch.cuda.set_device(0)
+    return torch
+
+
+def _timelapse_pairs(frames, misses):
+    """pairs in the reference's loop order (AxonDetections.py:553-566): (mask 0, source frame t_bef, target frame t)"""
+    spec = []
+    for t in range(len(frames)):
+        for tb in range(t - 1, t - (misses + 2), -1):
+            if tb >= 0:
+                spec.append((0, tb, t))
+    return spec
+
+
+def _run_and_check(torch, mask, frames, spec, max_px, tag):
+    from axtrack_b200 import ops
+    offs = np.concatenate([[0], np.cumsum([len(f) for f in frames])])
+    dets = np.concatenate(frames).astype(np.int32).reshape(-1, 2)
+    pairs, total, _ = ops.make_pairs([(mk, int(offs[a]), len(frames[a]), int(offs[b]), len(frames[b])) for mk, a, b in spec])
+    masks = mask if mask.ndim == 3 else mask[None]
+    bits = ops.pack_mask(torch.from_numpy(np.ascontiguousarray(masks, dtype=np.uint8)).cuda())
+    pl, un, wc, _ = ops.cost_matrix_batch(bits, masks.shape[2], torch.from_numpy(dets).cuda(), pairs, max_px)
+    ops.raise_status()
+    pl, un, wc = pl.cpu().numpy(), un.cpu().numpy(), wc.cpu().numpy()
+    n_reached = 0
+    for (mk, a, b), pd in zip(spec, pairs):
+        o, ns, nd = int(pd['out_off']), int(pd['n_src']), int(pd['n_dst'])
+        if ns * nd == 0:
+            continue
+        ref = oracle.cost_matrix_rule(masks[mk].astype(bool), frames[a], frames[b], max_px)
+        got_pl, got_un = pl[o:o + ns * nd].reshape(ns, nd), un[o:o + ns * nd].reshape(ns, nd)
+        bad = np.argwhere((got_pl != ref[0].reshape(ns, nd)) | (got_un != ref[1].reshape(ns, nd)))
+        assert len(bad) == 0, (tag, (a, b), bad[:5].tolist(), got_pl[tuple(bad[0])], ref[0].reshape(ns, nd)[tuple(bad[0])])
+        ok = got_un == 0
+        got_wc = wc[o:o + ns * nd].reshape(ns, nd)
+        assert np.all(np.isinf(got_wc[~ok])), tag
+        assert np.allclose(got_wc[ok], np.asarray(ref[2]).reshape(ns, nd)[ok], rtol=1e-5, atol=0), tag
+        n_reached += int(ok.sum())
+    return n_reached
+
+
+def _islands_mask(H, W, seed):
+    """Corridors cut into pieces + blobs of every size + speckle: components well below and above max_px."""
+    rng = np.random.default_rng(seed)
+    m = synth.make_mask(H, W, seed, pitch=(30, 70), width=(3, 8)).astype(bool)
+    for _ in range(40):                                     # cuts
+        y, x = rng.integers(0, H), rng.integers(0, W)
+        if rng.random() < 0.5:
+            m[y:y + 3, :] = False
+        else:
+            m[:, x:x + 3] = False
+    for _ in range(30):                                     # blobs
+        y, x, h, w = rng.integers(0, H - 12), rng.integers(0, W - 12), rng.integers(1, 12), rng.integers(1, 12)
+        m[y:y + h, x:x + w] = True
+    m |= rng.random((H, W)) < 0.02                          # speckle
+    return m
+
+
+def _frames_on(mask, n_frames, n, seed, off_frac):
+    rng = np.random.default_rng(seed)
+    fg = np.argwhere(mask)
+    H, W = mask.shape
+    out = []
+    for t in range(n_frames):
+        d = fg[rng.integers(0, len(fg), n)]
+        jit = rng.integers(-2, 3, (n, 2)) * (rng.random((n, 1)) < off_frac)
+        d = d + jit
+        d[:, 0] = np.clip(d[:, 0], 0, H - 1); d[:, 1] = np.clip(d[:, 1], 0, W - 1)
+        out.append(d.astype(np.int32))
+    return out
+
+
+@pytest.mark.parametrize('seed,max_px,misses', [(0, 60, 1), (1, 35, 1), (2, 90, 2), (3, 60, 2), (4, 20, 1)])
+def test_cover_on_island_masks(cuda, seed, max_px, misses):
+    H, W = 260, 300
+    mask = _islands_mask(H, W, seed)
+    frames = _frames_on(mask, 7, 40, seed + 10, off_frac=0.3)
+    frames[4] = frames[4][:0]                               # an empty frame in the middle
+    frames[2] = np.vstack([frames[2], frames[1][:5]])       # detections that coincide with those of a neighbour frame
+    n = _run_and_check(cuda, mask, frames, _timelapse_pairs(frames, misses), max_px, ('islands', seed))
+    assert n > 50
+
+
+def test_cover_on_a_connected_corridor_mask(cuda):
+    """The regime of the real data: one component that reaches far beyond max_px; no directed search is needed
+    except for off-mask detections."""
+    H, W = 700, 900
+    mask = synth.make_mask(H, W, 5, pitch=(60, 130), width=(4, 10)).astype(bool)
+    tracks = synth.make_tracks(mask, 60, 8, 5, off_mask_frac=0.1)
+    n = _run_and_check(cuda, mask, [t.astype(np.int32) for t in tracks], _timelapse_pairs(tracks, 1), 300, 'corridor')
+    assert n > 500
+
+
+def test_cover_with_pairs_in_any_order_and_duplicates(cuda):
+    """The cover is decided from the pair list alone: shuffled pairs, a pair given twice, both directions of a
+    pair, a frame paired with itself."""
+    H, W = 200, 240
+    mask = _islands_mask(H, W, 11)
+    frames = _frames_on(mask, 6, 30, 12, off_frac=0.25)
+    spec = _timelapse_pairs(frames, 1)
+    rng = np.random.default_rng(0)
+    spec = [spec[i] for i in rng.permutation(len(spec))]
+    spec += [(0, 1, 2), (0, 2, 1), (0, 3, 3), (0, 5, 0)]
+    n = _run_and_check(cuda, mask, frames, spec, 70, 'shuffled')
+    assert n > 50
+
+
+def test_cover_wide_radius(cuda):
+    """max_px > 511: the 256-column kernels take the same chains."""
+    H, W = 900, 1500
+    mask = synth.make_mask(H, W, 7, pitch=(90, 200), width=(4, 9)).astype(bool)
+    mask[:, 700:704] = False                                 # two halves: components that do not reach max_px everywhere
+    tracks = synth.make_tracks(mask, 16, 5, 7, off_mask_frac=0.15)
+    n = _run_and_check(cuda, mask, [t.astype(np.int32) for t in tracks], _timelapse_pairs(tracks, 1), 700, 'wide')
+    assert n > 30
+
+
+def test_errors_inside_reverse_pairs(cuda):
+    """An out-of-grid detection in a frame that is only a TARGET side of the search still raises the reference's error,
+    first offender in the reference's order, with start / goal the right way round."""
+    from axtrack_b200 import ops
+    m = np.ones((50, 60), np.uint8)
+    bits = ops.pack_mask(cuda.from_numpy(m).cuda())
+    # frames 0..3 of two detections each; pairs (1,0) (2,0) (2,1) (3,1) (3,2): frame 0 is not searched
+    spec = [(0, 0, 2, 2, 2), (0, 0, 2, 4, 2), (0, 2, 2, 4, 2), (0, 2, 2, 6, 2), (0, 4, 2, 6, 2)]
+    pairs, total, nsrc = ops.make_pairs(spec)
+    base = np.array([[5, 5], [8, 3], [6, 6], [7, 7], [9, 9], [10, 4], [11, 11], [12, 5]], np.int32)
+    for idx, bad, msg in [(1, (50, 3), r'Start of \(50, 3\) lies outside grid'),       # a source of the unsearched frame 0
+                          (0, (-1, 5), r'Start of \(-1, 5\) lies outside grid'),
+                          (3, (7, 60), r'Goal of \(7, 60\) lies outside grid'),          # frame 1: goal of pair (1,0) comes first
+                          (7, (12, -2), r'Goal of \(12, -2\) lies outside grid')]:
+        dets = base.copy()
+        dets[idx] = bad
+        ops.cost_matrix_batch(bits, 60, cuda.from_numpy(dets).cuda(), pairs, 500)
+        with pytest.raises(ValueError, match=msg):
+            ops.raise_status(pairs, dets)
+        ops.raise_status()
+
+
+def test_components_kernel_vs_scipy(cuda):
+    """axb_components.cu through its effect: on a mask of islands, a pair answered in reverse equals the oracle for
+    every max_px around the islands' sizes (the extents decide None vs directed search)."""
+    from scipy import ndimage
+    H, W = 120, 150
+    rng = np.random.default_rng(21)
+    mask = np.zeros((H, W), bool)
+    for k in range(14):                                      # diagonal, L-shaped and straight islands of growing size
+        y, x = 6 + 8 * k, 5 + rng.integers(0, 20)
+        L = 6 + 7 * k
+        mask[y:y + 2, x:min(W - 1, x + L)] = True
+        if k % 3 == 0:
+            mask[max(0, y - 4):y, x:x + 2] = True
+    lab, ncomp = ndimage.label(mask)
+    assert ncomp >= 10
+    frames = _frames_on(mask, 4, 45, 22, off_frac=0.2)
+    for max_px in (8, 15, 30, 55, 100):
+        _run_and_check(cuda, mask, frames, _timelapse_pairs(frames, 1), max_px, ('extents', max_px))
