@@ -39,6 +39,9 @@ struct axb_ctx {
     int* comp_label = nullptr;        size_t comp_label_bytes = 0;      // mask components (axb_components.cu)
     int4* comp_ext = nullptr;         size_t comp_ext_bytes = 0;
     int dense_stride = 0;
+    int* early_list = nullptr;        size_t early_list_bytes = 0;      // in-grid off-mask detections: the all-levels kernel runs them beside the level-0 kernels
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     uint8_t* trace_par = nullptr;                                      // K4: per general CTA entry directions
     int* trace_iota = nullptr;        size_t trace_iota_bytes = 0;
     uint32_t* k2_tiles = nullptr;     size_t k2_tiles_bytes = 0;       // 8x4-pixel tile words of the masks of the current call
@@ -115,6 +118,12 @@ int ensure_k2(axb_ctx* c, int n_pairs, int total_src) {
     if (rc != AXB_OK) return rc;
     c->dense_stride = (int)(c->dense_list_bytes / (2 * sizeof(int)));
     if ((rc = grow(c, &c->dir_list, &c->dir_list_bytes, n_items * sizeof(int))) != AXB_OK) return rc;
+    if ((rc = grow(c, &c->early_list, &c->early_list_bytes, n_items * sizeof(int))) != AXB_OK) return rc;
+    if (!c->side_stream) {
+        AXB_CUDA(c, cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking));
+        AXB_CUDA(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+        AXB_CUDA(c, cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+    }
     if ((rc = grow(c, &c->item_bits, &c->item_bits_bytes, (n_items + 31) / 32 * sizeof(uint32_t))) != AXB_OK) return rc;
     return grow(c, &c->gen_list, &c->gen_list_bytes, n_items * sizeof(int));
 }
@@ -133,6 +142,7 @@ void set_prep(axb::K2Params& p, const axb::K2Prep& o, axb_ctx* c) {
     p.work_prefix = o.work_prefix; p.all_prefix = o.all_prefix; p.next_same = o.next_same; p.p1_prefix = o.p1_prefix;
     p.rev_head = o.rev_head; p.rev_next = o.rev_next; p.lead_of = o.lead_of; p.item_bits = o.item_bits;
     p.dir_list = c->dir_list; p.gen_list = c->gen_list; p.dense_list = c->dense_list; p.counters = c->counters;
+    p.gen_src = c->gen_list; p.gen_len_ctr = axb::kCtrGenLen; p.gen_ticket_ctr = axb::kCtrGenTicket;
 }
 
 // where a fast-kernel launch takes its items from / puts the windows it cannot hold
@@ -175,12 +185,15 @@ void axb_destroy(axb_ctx* c) {
     cudaDeviceSynchronize();
     if (c->alt) { axb_destroy(c->alt); c->alt = nullptr; }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->side_stream) cudaStreamDestroy(c->side_stream);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->ev_in) cudaEventDestroy(c->ev_in);
     for (int i = 0; i < 2; ++i) if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
     cudaFree(c->status_dev); cudaFreeHost(c->status_host);
     cudaFree(c->k2_fast_scratch); cudaFree(c->k2_gen_scratch); cudaFree(c->counters); cudaFree(c->prefix_dev);
     cudaFree(c->trace_par); cudaFree(c->trace_iota); cudaFree(c->k2_wide_scratch); cudaFree(c->trace_par_wide);
-    cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->dir_list); cudaFree(c->item_bits); cudaFree(c->comp_label); cudaFree(c->comp_ext); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
+    cudaFree(c->gen_list); cudaFree(c->dense_list); cudaFree(c->dir_list); cudaFree(c->early_list); cudaFree(c->item_bits); cudaFree(c->comp_label); cudaFree(c->comp_ext); cudaFree(c->k2_tiles); cudaFree(c->k1_scratch);
     cudaFree(c->st_mask); cudaFree(c->st_bits); cudaFree(c->st_dets); cudaFree(c->st_pairs);
     cudaFree(c->st_plen); cudaFree(c->st_unr); cudaFree(c->st_wc); cudaFree(c->st_k1); cudaFree(c->k6_flags);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -302,6 +315,22 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
     p.orig_base = orig_base;
     p.comp_label = cover ? c->comp_label : nullptr; p.comp_ext = cover ? c->comp_ext : nullptr;
+    // In-grid off-mask detections (a few per cent on real data) need the all-levels kernel, one search latency each:
+    // it takes them on a side stream while the level-0 kernels run (k2_classify_kernel).  AXB_K2_NO_EARLY: A/B timing.
+    static const bool no_early = getenv("AXB_K2_NO_EARLY") != nullptr;
+    const bool early = !no_early && n_pairs >= 2;
+    p.early = early ? 1 : 0;
+    const int gen_grid = std::max(1, std::min(c->k2_gen_ctas * (wide ? axb::kWideCtasPerSm : 1), total_src));
+    if (early) {
+        axb::launch_k2_classify(p, c->early_list, total_src, s);
+        AXB_CUDA(c, cudaEventRecord(c->ev_fork, s));
+        AXB_CUDA(c, cudaStreamWaitEvent(c->side_stream, c->ev_fork, 0));
+        axb::K2Params pe = p;
+        pe.gen_src = c->early_list; pe.gen_len_ctr = axb::kCtrEarlyLen; pe.gen_ticket_ctr = axb::kCtrEarlyTicket;
+        axb::launch_k2_general(pe, gen_grid, c->side_stream);
+        AXB_CUDA(c, cudaEventRecord(c->ev_join, c->side_stream));
+        c->launches += 2;
+    }
     int* const dense_a = c->dense_list;
     int* const dense_b = c->dense_list + c->dense_stride;
     // The launches of a call: (1) level-0 search from every detection of the searched sets, with the reverse members of
@@ -329,7 +358,8 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
                 c->launches += 2;
             }
         }
-        axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas * axb::kWideCtasPerSm, total_src)), s);
+        if (early) AXB_CUDA(c, cudaStreamWaitEvent(s, c->ev_join, 0));      // one scratch set: the late list after the early one
+        axb::launch_k2_general(p, gen_grid, s);
         c->launches += 5;
         AXB_CUDA(c, cudaGetLastError());
         static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;     // profiling aid: where the work items went
@@ -337,8 +367,8 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
             int h[16];
             cudaStreamSynchronize(s);
             cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
-            fprintf(stderr, "[axb] wide K2: %d sources, %d first-pass tickets, %d to the second kind, %d directed, %d to the all-levels kernel\n",
-                    total_src, h[0], h[3], h[5], h[1]);
+            fprintf(stderr, "[axb] wide K2: %d sources, %d first-pass tickets, %d to the second kind, %d directed, all-levels kernel: %d early + %d late\n",
+                    total_src, h[0], h[3], h[5], h[9], h[1]);
         }
         return AXB_OK;
     }
@@ -359,7 +389,8 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
         axb::launch_k2_fast(p, gd, s);
         c->launches += 2;
     }
-    axb::launch_k2_general(p, std::max(1, std::min(c->k2_gen_ctas, total_src)), s);
+    if (early) AXB_CUDA(c, cudaStreamWaitEvent(s, c->ev_join, 0));          // one scratch set: the late list after the early one
+    axb::launch_k2_general(p, gen_grid, s);
     c->launches += 5;
     AXB_CUDA(c, cudaGetLastError());
     static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;
@@ -367,8 +398,8 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
         int h[16];
         cudaStreamSynchronize(s);
         cudaMemcpy(h, c->counters, sizeof h, cudaMemcpyDeviceToHost);
-        fprintf(stderr, "[axb] K2: %d sources, %d first-pass tickets, %d dense windows, %d directed (+%d dense), %d to the all-levels kernel\n",
-                total_src, h[0], h[3], h[5], h[7], h[1]);
+        fprintf(stderr, "[axb] K2: %d sources, %d first-pass tickets, %d dense windows, %d directed (+%d dense), all-levels kernel: %d early + %d late\n",
+                total_src, h[0], h[3], h[5], h[7], h[9], h[1]);
     }
     return AXB_OK;
 }

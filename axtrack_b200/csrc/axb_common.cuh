@@ -40,7 +40,7 @@ constexpr int kFastGQCap = 2048;      // per-CTA global overflow frontier entrie
 constexpr int kFastQCap = 384;        // frontier entries (tile word, bits: 8 B) per buffer in shared memory
 constexpr int kFastCtasPerSm = 3;
 // sparse window (only the non-zero tile words + a presence/base table): 10 CTAs per SM
-constexpr int kSparseWords = 3904;    // non-zero tile words a sparse window can hold (15.25 KB; with the tables, queues and control block 10 CTAs fill an SM at max_px = 500)
+constexpr int kSparseWords = 3896;    // non-zero tile words a sparse window can hold (15.25 KB; with the tables, queues and control block 10 CTAs fill an SM at max_px = 500)
 constexpr int kSparseQCap = 144;
 constexpr int kSparseHash = 512;
 constexpr int kSparseHashMaxLoad = 320;
@@ -101,6 +101,10 @@ struct K2Params {
     int src_len_ctr, src_ticket_ctr;
     int* dense_out;
     int dense_out_ctr;
+    // the all-levels kernel's work list
+    const int* gen_src;
+    int gen_len_ctr, gen_ticket_ctr;
+    int early;                   // in-grid off-mask detections were handed to the all-levels kernel before the level-0 kernels ran
 };
 
 // outputs of k2_prep_kernel (each [n_pairs + 1] ints)
@@ -112,9 +116,9 @@ struct K2Prep {
 constexpr int kPrepArrays = 9;
 
 // counters[]: [0] first-pass ticket, [1] general list length, [2] general ticket, [3] dense list A length, [4] its ticket,
-// [5] directed list length, [6] its ticket, [7] dense list B length, [8] its ticket
+// [5] directed list length, [6] its ticket, [7] dense list B length, [8] its ticket, [9] early list length, [10] its ticket
 enum { kCtrP1Ticket = 0, kCtrGenLen = 1, kCtrGenTicket = 2, kCtrDenseALen = 3, kCtrDenseATicket = 4, kCtrDirLen = 5,
-       kCtrDirTicket = 6, kCtrDenseBLen = 7, kCtrDenseBTicket = 8 };
+       kCtrDirTicket = 6, kCtrDenseBLen = 7, kCtrDenseBTicket = 8, kCtrEarlyLen = 9, kCtrEarlyTicket = 10 };
 
 inline int k2_tile_rows(int max_px) { return (max_px + 3) / 4 + 1; }
 inline size_t k2_fast_smem_bytes(int max_px) {      // dense window + queues + hash
@@ -157,6 +161,7 @@ void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint
 void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_sparse_wide(const K2Params& p, int grid, bool second, cudaStream_t stream);   // max_px 512 .. 1023
+void launch_k2_classify(const K2Params& p, int* early, int total_src, cudaStream_t stream);
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);     // max_px > kFastMaxPx: the wide kernel
 void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);

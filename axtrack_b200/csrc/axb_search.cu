@@ -34,6 +34,7 @@
 //                           bitmaps in the CTA's global scratch, every source.
 //   k2_prep_kernel          chains, work prefix sums, counter reset (one CTA, tiny).
 #include "axb_common.cuh"
+#include <algorithm>
 
 namespace axb {
 
@@ -440,14 +441,14 @@ __device__ bool run_item(const K2Params& p, const int item, uint32_t* smem, uint
 template <bool WIDE>
 __device__ __forceinline__ void general_body(const K2Params& p, uint32_t* smem, Ctl& ctl) {
     uint32_t* const gscr = p.gen_scratch + (size_t)blockIdx.x * Geo<WIDE>::SCRATCH;
-    const int total = p.counters[1];
+    const int total = p.counters[p.gen_len_ctr];
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[2], 1);
+        if (threadIdx.x == 0) ctl.item = atomicAdd(&p.counters[p.gen_ticket_ctr], 1);
         __syncthreads();
         const int t = ctl.item;
         if (t >= total) break;
-        const int item = p.gen_list[t];
+        const int item = p.gen_src[t];
         run_item<true, WIDE ? kK2Threads : kGenThreads, WIDE>(p, item, smem, gscr, ctl);
         if (p.trace_par) {             // one (source, target) request per pair: walk the entry directions back
             __syncthreads();
@@ -688,6 +689,32 @@ void launch_k2_prep(const axb_pair_desc* pairs, int n_pairs, const K2Prep& o, in
     lim.n_masks = n_masks; lim.n_dets = n_dets; lim.out_capacity = out_capacity; lim.total_src = total_src; lim.allow_reverse = allow_reverse;
     const size_t smem = n_pairs <= kPrepSmemPairs ? 5 * (size_t)n_pairs * sizeof(int) : 0;
     k2_prep_kernel<<<1, 1024, smem, stream>>>(pairs, n_pairs, o, counters, lim, err_flags);
+}
+
+// Work items whose detection lies in the grid but off the mask: level 0 is at most their four neighbours, the
+// all-levels kernel takes them from the start (list `early`), concurrently with the level-0 kernels, which skip
+// the forward members of such items and leave their rows alone.
+__global__ void __launch_bounds__(256) k2_classify_kernel(const K2Params p, int* __restrict__ early) {
+    const int total = p.work_prefix[p.n_pairs];
+    for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < total; item += gridDim.x * blockDim.x) {
+        int lo = 0, hi = p.n_pairs - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (p.work_prefix[mid] <= item) lo = mid; else hi = mid - 1;
+        }
+        const axb_pair_desc lead = p.pairs[lo];
+        const size_t d = (size_t)lead.src_off + (item - p.work_prefix[lo]);
+        const int y = p.dets_yx[2 * d], x = p.dets_yx[2 * d + 1];
+        if (y < 0 || y >= p.H || x < 0 || x >= p.W) continue;
+        if ((__ldg(p.mask_bits + ((size_t)lead.mask_idx * p.H + y) * p.Wp + (x >> 5)) >> (x & 31)) & 1u) continue;
+        atomicOr(&p.item_bits[item >> 5], 1u << (item & 31));
+        early[atomicAdd(&p.counters[kCtrEarlyLen], 1)] = item;
+    }
+}
+
+void launch_k2_classify(const K2Params& p, int* early, int total_src, cudaStream_t stream) {
+    const int grid = std::max(1, std::min((total_src + 255) / 256, 148 * 4));
+    k2_classify_kernel<<<grid, 256, 0, stream>>>(p, early);
 }
 
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream) {

@@ -34,6 +34,7 @@
 //   k2_fast_kernel    dense window (64.5 KB, 3 CTAs per SM) for the sources whose window has
 //                     more non-zero tile words than the sparse layout holds (dense masks).
 #include "axb_search_tiles.cuh"
+#include <cstdio>
 
 namespace axb {
 
@@ -70,9 +71,6 @@ void launch_k2_tiles(const uint32_t* mask_bits, int n_masks, int H, int Wp, uint
     k2_tile_mask_kernel<<<grid > 0 ? grid : 1, 256, 0, stream>>>(mask_bits, n_masks, H, Wp, tiles);
 }
 
-#ifdef AXB_TIMING
-__device__ unsigned long long g_dbg[24];   // cycles: [0] setup+candidates [1] staging [2] waves; [3] #waves [4] #items [5] entries [6] warp-0 wave body [7] barrier; [8..] pooled kernel phases
-#endif
 
 namespace {
 
@@ -167,6 +165,8 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
     w.ty0 = sy >> 2; w.tx0 = (sx >> 5) * 4;
     const bool src_in = sy >= 0 && sy < p.H && sx >= 0 && sx < p.W;
     const bool src_on = src_in && ((__ldg(p.mask_bits + ((size_t)lead.mask_idx * p.H + sy) * p.Wp + (sx >> 5)) >> (sx & 31)) & 1u);
+    const bool pre = p.early && src_in && !src_on;          // the all-levels kernel has this item's forward members already (k2_classify_kernel)
+    if (pre && !revmask) return kItemDone;
     const long long r2 = (long long)RW * RW;
     constexpr int kPassLoad = C::kMaxLoad > NT ? C::kMaxLoad - NT : 0;
 
@@ -184,13 +184,18 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
             if (t < total_t) {
                 while (m + 1 < nm && t >= ch.cum[m + 1]) ++m;
                 j = t - ch.cum[m];
-                const bool rev = (revmask >> m) & 1u;
+            }
+            const bool rev = (revmask >> m) & 1u;
+            if (t < total_t && (rev || !pre)) {
                 const int ty = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j)];
                 const int tx = p.dets_yx[2 * ((size_t)ch.dst_off[m] + j) + 1];
+                const bool t_in = ty >= 0 && ty < p.H && tx >= 0 && tx < p.W;
+                // reverse member whose other detection is off the mask: its whole row belongs to the all-levels kernel
+                const bool foreign = rev && p.early && t_in &&
+                                     !((__ldg(p.mask_bits + ((size_t)ch.mask_idx * p.H + ty) * p.Wp + (tx >> 5)) >> (tx & 31)) & 1u);
                 dy = ty - sy; dx = tx - sx;
                 const long long d2 = (long long)dy * dy + (long long)dx * dx;
-                if (d2 < r2) {                                        // AxonDetections.py:620-623
-                    const bool t_in = ty >= 0 && ty < p.H && tx >= 0 && tx < p.W;
+                if (d2 < r2 && !foreign) {                            // AxonDetections.py:620-623
                     // the reference's start is this detection (forward) or the other one (reverse member)
                     const bool start_in = rev ? t_in : src_in, goal_in = rev ? src_in : t_in;
                     const unsigned long long ek = rev ? (((unsigned long long)(p.orig_base + ch.ebase[m] + j) << 26) | ((unsigned long long)si << 2))
@@ -213,10 +218,12 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                         }
                     }
                 }
-                const long long oo = ch.orow[m] + (long long)j * ch.ostride[m];
-                p.path_len[oo] = self ? 1 : RW;                       // None -> max_px (AxonDetections.py:736)
-                p.unreachable[oo] = self ? 0 : 1;
-                if (p.wcost) p.wcost[oo] = self ? 0.f : __int_as_float(0x7f800000);
+                if (!foreign) {
+                    const long long oo = ch.orow[m] + (long long)j * ch.ostride[m];
+                    p.path_len[oo] = self ? 1 : RW;                   // None -> max_px (AxonDetections.py:736)
+                    p.unreachable[oo] = self ? 0 : 1;
+                    if (p.wcost) p.wcost[oo] = self ? 0.f : __int_as_float(0x7f800000);
+                }
             }
             if (revmask) {
                 const uint32_t cb = __ballot_sync(kFull, chk);
@@ -577,6 +584,12 @@ void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream) {
         } else {
             q.hash_smem = 0;
         }
+    }
+    static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;
+    if (dbg) {
+        int nb = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k2_sparse_kernel, kFastThreads, smem);
+        fprintf(stderr, "[axb] k2_sparse_kernel: grid %d, %zu B dynamic shared memory, %d window words, %d CTAs per SM\n", grid, smem, q.sparse_words, nb);
     }
     k2_sparse_kernel<<<grid, kFastThreads, smem, stream>>>(q);
 }

@@ -138,7 +138,7 @@ __device__ __forceinline__ void row_half_widths(const Win& w, int tr, int& hw_in
 }  // namespace
 
 #ifdef AXB_TIMING
-extern __device__ unsigned long long g_dbg[24];   // cycles: [0] setup+candidates [1] staging [2] waves; [3] #waves [4] #items [5] entries [6] warp-0 wave body [7] barrier
+__device__ unsigned long long g_dbg[24];       // (this header has one includer)   // cycles: [0] setup+candidates [1] staging [2] waves; [3] #waves [4] #items [5] entries [6] warp-0 wave body [7] barrier
 #define AXB_T(k, t0) do { if (threadIdx.x == 0) { const long long t1_ = clock64(); atomicAdd(&g_dbg[k], (unsigned long long)(t1_ - t0)); t0 = t1_; } } while (0)
 #define AXB_C(k, v) do { if (threadIdx.x == 0) atomicAdd(&g_dbg[k], (unsigned long long)(v)); } while (0)
 // phase timer of the per-warp search: the clock is read after `dep` is available (scoreboard wait)
