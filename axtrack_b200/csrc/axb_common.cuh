@@ -23,7 +23,7 @@ constexpr int kMaxRev = 4;            // pairs answered from their TARGET side b
 constexpr int kMaxMem = kMaxChain + kMaxRev;
 constexpr int kHashSize = 1024;       // target-cell hash (u32 entries) in shared memory
 constexpr int kHashMaxLoad = 640;     // candidates per search pass
-constexpr int kCandCap = 1024;        // per-CTA global candidate table (>= kHashMaxLoad)
+constexpr int kCandCap = 2048;        // per-CTA global candidate table (>= the hash loads)
 constexpr int kK2Threads = 256;       // wide all-levels kernel: one CTA (8 warps) per source search
 constexpr int kGenThreads = 512;      // all-levels kernel (one CTA per SM): 16 warps per source search
 constexpr int kSeedCal = 512;         // general kernel: per-j seed calendar entries (j <= max_px)
@@ -46,11 +46,11 @@ constexpr int kSparseHash = 512;
 constexpr int kSparseHashMaxLoad = 320;
 constexpr int kSparseCtasPerSm = 10;
 // sparse window on the 256-column circle (max_px 512 .. 1023): 2 CTAs per SM
-constexpr int kWideWords = 20480;     // non-zero tile words a wide sparse window can hold (80 KB; the whole diamond: 65 792)
+constexpr int kWideWords = 19456;     // non-zero tile words a wide sparse window can hold (76 KB; the whole diamond: 65 792)
 constexpr int kWideQCap = 384;
 constexpr int kWideSparseCtasPerSm = 2;
-constexpr int kWideHash = 1024;       // target hash of the wide sparse kernel (shared memory)
-constexpr int kWideHashMaxLoad = 512;
+constexpr int kWideHash = 2048;       // target hash of the wide sparse kernel (shared memory): a radius of 1000 px holds four times the targets,
+constexpr int kWideHashMaxLoad = 1280; // and the chains of the cover twice as many again; a second pass is a second search
 // general kernel (all levels): both bitmaps, 1 CTA per SM
 constexpr int kGenQCap = 2048;
 constexpr int kGCap = 1 << 19;        // >= cells of the window: worst-case frontier / seed lists
@@ -136,7 +136,7 @@ inline size_t k2_gen_smem_bytes(int max_px) {
 inline size_t k2_gen_wide_smem_bytes() {            // bitmaps in global scratch
     return (2 * (size_t)kGenQCap + kHashSize + 2 * kSeedCalWide) * sizeof(uint32_t);
 }
-constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap + kSparseHash;
+constexpr size_t kFastScratchWords = (size_t)kCandCap + 4 * (size_t)kFastGQCap + kSparseHash + kCandCap / 4;   // candidates | overflow queues | sparse target hash | cell bit of a candidate (bytes)
 constexpr size_t kTraceParBytes = (size_t)(kFastMaxPx + 1) * kRowBits;
 constexpr size_t kTraceParBytesWide = (size_t)(AXB_MAX_PX + 1) * 2 * kRowBits;
 constexpr size_t kGenScratchWords = (size_t)kCandCap + 4 * (size_t)kGCap;

@@ -241,7 +241,9 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                     int bit;
                     const uint32_t key = cell_key<LOGC>(dy, dx, w.oy, w.ox, NR, bit);
                     AXB_ASSERT(((key & G::WMASK) >> LOGC) < (uint32_t)NR && bit >= 0 && bit < 32 && slot < (1u << G::SLOTB));
-                    const uint32_t entry = (key << G::ESH) | ((uint32_t)bit << G::SLOTB) | slot;
+                    uint32_t entry = (key << G::ESH) | slot;
+                    if (G::BIT_IN_ENTRY) entry |= (uint32_t)bit << G::SLOTB;
+                    else reinterpret_cast<uint8_t*>(gscr + kCandCap + 4 * (size_t)kFastGQCap + kSparseHash)[slot] = (uint8_t)bit;
                     uint32_t h = hash_slot<HASH>(key);
                     while (atomicCAS(&hash[h], kEmpty, entry) != kEmpty) h = (h + 1) & (HASH - 1);
                 }

@@ -29,8 +29,9 @@ template <int LOGC> struct TW {
     static constexpr uint32_t WMASK = (1u << WB) - 1u;
     static constexpr uint32_t HALFBIT = 1u << WB;        // key of a tile word = half << WB | word index
     static constexpr int KB = WB + 1;                    // key bits: 16 / 18
-    static constexpr int ESH = 32 - KB;                  // target-hash entry = key << ESH | bit << SLOTB | candidate slot
-    static constexpr int SLOTB = ESH - 5;                // 11 / 9 bits of candidate slot
+    static constexpr int ESH = 32 - KB;                  // target-hash entry = key << ESH | bit << SLOTB | candidate slot (128 columns) ...
+    static constexpr bool BIT_IN_ENTRY = ESH >= 16;      // ... or key << ESH | candidate slot, the cell's bit in a byte table of the CTA's scratch (256 columns)
+    static constexpr int SLOTB = BIT_IN_ENTRY ? ESH - 5 : ESH;   // 11 / 14 bits of candidate slot
     static constexpr int GROUPS = TC / 32;               // presence-table entries per folded row
 };
 static_assert(TW<7>::HALFBIT == 0x8000u && TW<7>::ESH == 16 && TW<7>::SLOTB == 11, "the 128-column layout of round 1");
@@ -58,9 +59,10 @@ __device__ __forceinline__ uint32_t cell_key(int dy, int dx, int oy, int ox, int
 }
 
 template <int HASH> __device__ __forceinline__ uint32_t hash_slot(uint32_t key);
+template <> __device__ __forceinline__ uint32_t hash_slot<2048>(uint32_t key) { return (key * 0x9E3779B1u) >> 21; }
 template <> __device__ __forceinline__ uint32_t hash_slot<1024>(uint32_t key) { return (key * 0x9E3779B1u) >> 22; }
 template <> __device__ __forceinline__ uint32_t hash_slot<512>(uint32_t key) { return (key * 0x9E3779B1u) >> 23; }
-static_assert(kCandCap <= 2048 && kSparseHashMaxLoad <= 512, "hash entries keep 11 (wide layout: 9) bits of candidate slot");
+static_assert(kCandCap <= 2048 && kSparseHashMaxLoad <= 512, "hash entries keep 11 (wide layout: 14) bits of candidate slot");
 
 // Members of a chain: forward pairs (this source's row of the pair's matrix, targets = the pair's dst detections)
 // and reverse pairs (k2_prep_kernel "cover": this detection is a TARGET of the pair; the search answers its column,
@@ -167,7 +169,7 @@ template <> struct Cfg<true, 8> {      // max_px 512 .. 1023: about twice the fr
     static constexpr int kQCap = kWideQCap, kHash = kWideHash, kMaxLoad = kWideHashMaxLoad;
 };
 static_assert(kFastQCap / kNW + kGSeg < 0x8000 && kWideQCap / kWideNW + kFastGQCap / kWideNW < 0x8000, "the per-warp wave counter keeps 15 bits of entries");
-static_assert(kWideHashMaxLoad <= (1 << TW<8>::SLOTB) && kWideHashMaxLoad <= kCandCap, "wide hash entries keep 9 bits of candidate slot");
+static_assert(kWideHashMaxLoad <= (1 << TW<8>::SLOTB) && kWideHashMaxLoad <= kCandCap, "wide hash entries keep 14 bits of candidate slot");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -241,8 +243,10 @@ __device__ __noinline__ int probe_settle(const K2Params& p, const uint32_t* hash
     for (;;) {
         const uint32_t e = hash[h];
         if (e == kEmpty) break;
-        if ((e >> G::ESH) == key && ((claimed >> ((e >> G::SLOTB) & 31u)) & 1u)) {
-            const uint32_t c = cand[e & ((1u << G::SLOTB) - 1u)];
+        const uint32_t slot = e & ((1u << G::SLOTB) - 1u);
+        if ((e >> G::ESH) == key &&
+            ((claimed >> (G::BIT_IN_ENTRY ? (e >> G::SLOTB) & 31u : (uint32_t)reinterpret_cast<const uint8_t*>(cand + kCandCap + 4 * (size_t)kFastGQCap + kSparseHash)[slot])) & 1u)) {
+            const uint32_t c = cand[slot];
             const long long o = ch.orow[c >> 29] + (long long)(c & 0x0FFFFFFFu) * ch.ostride[c >> 29];
             p.path_len[o] = j + 1;
             p.unreachable[o] = 0;

@@ -174,3 +174,40 @@ def test_components_kernel_vs_scipy(cuda):
     frames = _frames_on(mask, 4, 45, 22, off_frac=0.2)
     for max_px in (8, 15, 30, 55, 100):
         _run_and_check(cuda, mask, frames, _timelapse_pairs(frames, 1), max_px, ('extents', max_px))
+
+
+_FULL_SIZE_SNIPPET = r'''
+import sys, zlib, numpy as np, torch
+sys.path.insert(0, '.')
+import bench
+from axtrack_b200 import ops, pipeline
+wl = dict(bench.WORKLOADS['c2'], T=14)
+mask, Y, tt, t0 = bench.make_block(wl)[:4]
+dev = torch.device('cuda', 0)
+bits = ops.pack_mask(torch.from_numpy(mask.astype(np.uint8)).to(dev))
+det = ops.decode_nms(torch.from_numpy(Y).to(dev), torch.from_numpy(tt).to(dev))
+n_out = det['n_out'].cpu().numpy(); cap = det['conf'].shape[1]
+for max_px in (500, 800):
+    pairs, total, _ = pipeline.build_pairs(n_out, cap, pipeline.frame_pair_keys(14))
+    pl, un, wc, _ = ops.cost_matrix_batch(bits, wl['W'], det['yx'].view(-1, 2), pairs, max_px)
+    ops.raise_status()
+    print('CRC', max_px, zlib.crc32(pl.cpu().numpy().tobytes()), zlib.crc32(un.cpu().numpy().tobytes()), zlib.crc32(wc.cpu().numpy().tobytes()), int((un == 0).sum()))
+'''
+
+
+def test_cover_equals_directed_searches_at_full_size(cuda):
+    """configs[1] shape (2048 x 2048, ~200 detections per frame, 14 frames), max_px 500 and 800: the cover with the
+    early all-levels launch gives bit for bit what one directed search per source gives (AXB_K2_NO_REVERSE,
+    AXB_K2_NO_EARLY are read once per process, hence the subprocesses)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for extra in ({}, {'AXB_K2_NO_REVERSE': '1', 'AXB_K2_NO_EARLY': '1'}):
+        env = dict(os.environ, **extra)
+        r = subprocess.run([sys.executable, '-c', _FULL_SIZE_SNIPPET], cwd=root, env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append([l for l in r.stdout.splitlines() if l.startswith('CRC')])
+    assert len(outs[0]) == 2 and outs[0] == outs[1], outs
+    assert int(outs[0][0].split()[-1]) > 10000
