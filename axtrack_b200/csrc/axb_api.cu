@@ -321,6 +321,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     const bool early = !no_early && n_pairs >= 2;
     p.early = early ? 1 : 0;
     const int gen_grid = std::max(1, std::min(c->k2_gen_ctas * (wide ? axb::kWideCtasPerSm : 1), total_src));
+    if (cover) { axb::launch_k2_fill_reverse(p, prep.dst_head, prep.state, s); c->launches += 1; }     // before the fork: the side stream overwrites rows of it
     if (early) {
         axb::launch_k2_classify(p, c->early_list, total_src, s);
         AXB_CUDA(c, cudaEventRecord(c->ev_fork, s));

@@ -162,6 +162,7 @@ void launch_k2_sparse(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_fast(const K2Params& p, int grid, cudaStream_t stream);
 void launch_k2_sparse_wide(const K2Params& p, int grid, bool second, cudaStream_t stream);   // max_px 512 .. 1023
 void launch_k2_classify(const K2Params& p, int* early, int total_src, cudaStream_t stream);
+void launch_k2_fill_reverse(const K2Params& p, const int* pair_searched, const int* state, cudaStream_t stream);
 void launch_k2_general(const K2Params& p, int grid, cudaStream_t stream);     // max_px > kFastMaxPx: the wide kernel
 void launch_k2_all_to_general(const int* work_prefix, int n_pairs, int* gen_list, int* counters, cudaStream_t stream);
 void launch_pack_mask_u8(const uint8_t* mask, int n_masks, int H, int W, uint32_t* bits, cudaStream_t s);

@@ -712,6 +712,28 @@ __global__ void __launch_bounds__(256) k2_classify_kernel(const K2Params p, int*
     }
 }
 
+// Matrices of the pairs that are answered from their target side: None everywhere, row-wise and coalesced (the
+// searches then store only what they settle; their own default stores would run down the columns, which matters
+// when the outputs live in another GPU's memory).  pair_searched[q] = 0 and state[q] >= 0: q is such a pair.
+__global__ void __launch_bounds__(256) k2_fill_reverse_kernel(const K2Params p, const int* __restrict__ pair_searched,
+                                                              const int* __restrict__ state) {
+    for (int q = blockIdx.y; q < p.n_pairs; q += gridDim.y) {
+        if (pair_searched[q] || state[q] < 0) continue;
+        const axb_pair_desc pd = p.pairs[q];
+        const long long n = (long long)pd.n_src * pd.n_dst;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+            p.path_len[pd.out_off + i] = p.max_px;
+            p.unreachable[pd.out_off + i] = 1;
+            if (p.wcost) p.wcost[pd.out_off + i] = __int_as_float(0x7f800000);
+        }
+    }
+}
+
+void launch_k2_fill_reverse(const K2Params& p, const int* pair_searched, const int* state, cudaStream_t stream) {
+    const dim3 grid(8, (unsigned)std::max(1, std::min(p.n_pairs, 148 * 4)));
+    k2_fill_reverse_kernel<<<grid, 256, 0, stream>>>(p, pair_searched, state);
+}
+
 void launch_k2_classify(const K2Params& p, int* early, int total_src, cudaStream_t stream) {
     const int grid = std::max(1, std::min((total_src + 255) / 256, 148 * 4));
     k2_classify_kernel<<<grid, 256, 0, stream>>>(p, early);

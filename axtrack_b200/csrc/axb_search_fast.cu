@@ -218,7 +218,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                         }
                     }
                 }
-                if (!foreign) {
+                if (!foreign && (!rev || self)) {                     // reverse members: None was filled in row-wise (k2_fill_reverse_kernel)
                     const long long oo = ch.orow[m] + (long long)j * ch.ostride[m];
                     p.path_len[oo] = self ? 1 : RW;                   // None -> max_px (AxonDetections.py:736)
                     p.unreachable[oo] = self ? 0 : 1;

@@ -13,7 +13,9 @@
  *     scratch of the calls in flight, so ONE ctx serves ONE stream at a time: issue the calls of a
  *     ctx on one stream (or order them yourself), and create one ctx per thread / per concurrent
  *     stream.  Every entry point selects the ctx's device and restores the calling thread's
- *     current device before it returns;
+ *     current device before it returns.  axb_cost_matrix_batch with two or more pairs forks part of its
+ *     work (the all-levels searches of off-mask detections) onto a ctx-owned side stream and joins it back
+ *     into `stream` before its last launch: the caller still sees one call ordered on `stream`;
  *   - the device-side status is sticky PER CTX until axb_status() reads it: a flag raised by one
  *     call (e.g. AXB_ERR_CAPACITY of axb_decode_nms) is reported by the next axb_status() or
  *     *_host entry point on that ctx, whichever comes first;
