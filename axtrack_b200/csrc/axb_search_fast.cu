@@ -220,6 +220,7 @@ __device__ int run_item_fast(const K2Params& p, const int item, uint32_t* smem, 
                 }
                 if (!foreign && (!rev || self)) {                     // reverse members: None was filled in row-wise (k2_fill_reverse_kernel)
                     const long long oo = ch.orow[m] + (long long)j * ch.ostride[m];
+                    AXB_ASSERT(oo >= 0 && m < nm && j >= 0 && j < ch.cum[m + 1] - ch.cum[m]);
                     p.path_len[oo] = self ? 1 : RW;                   // None -> max_px (AxonDetections.py:736)
                     p.unreachable[oo] = self ? 0 : 1;
                     if (p.wcost) p.wcost[oo] = self ? 0.f : __int_as_float(0x7f800000);
@@ -476,6 +477,7 @@ __device__ __forceinline__ int fetch_item(const K2Params& p, Ctl& ctl) {
                 if (p.p1_prefix[mid] <= t) lo = mid; else hi = mid - 1;
             }
             item = p.work_prefix[lo] + (t - p.p1_prefix[lo]);
+            AXB_ASSERT(t - p.p1_prefix[lo] < p.pairs[lo].n_src && item < p.work_prefix[p.n_pairs]);
         }
         ctl.item = item;
     }

@@ -216,7 +216,9 @@ __device__ __forceinline__ void sts64_if(uint32_t a, uint32_t x, uint32_t y, uin
 // 1: yes, 0: no, -1: (y, x) is off the mask.
 __device__ __forceinline__ int component_reaches(const K2Params& p, int mask_idx, int y, int x, int RW) {
     const size_t base = (size_t)mask_idx * p.H * p.W;
+    AXB_ASSERT(y >= 0 && y < p.H && x >= 0 && x < p.W);
     const int r = __ldg(p.comp_label + base + (size_t)y * p.W + x);
+    AXB_ASSERT(r < p.H * p.W);
     if (r < 0) return -1;
     const int4 e = __ldg(p.comp_ext + base + r);
     return max(max(e.x - (y + x), e.y - (y - x)), max(e.z - (x - y), e.w + (y + x))) >= RW ? 1 : 0;
@@ -226,6 +228,7 @@ __device__ __forceinline__ int component_reaches(const K2Params& p, int mask_idx
 // level-0 kernels again (directed list); off the mask its level 0 is at most its four neighbours, so straight to
 // the all-levels kernel.
 __device__ __forceinline__ void push_directed(const K2Params& p, int item, bool off_mask) {
+    AXB_ASSERT(item >= 0 && item < p.work_prefix[p.n_pairs]);
     const uint32_t bit = 1u << (item & 31);
     if (atomicOr(&p.item_bits[item >> 5], bit) & bit) return;
     if (off_mask) p.gen_list[atomicAdd(&p.counters[kCtrGenLen], 1)] = item;
