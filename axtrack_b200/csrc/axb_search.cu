@@ -513,7 +513,7 @@ __global__ void __launch_bounds__(256) k2_all_to_general_kernel(const int* __res
 // lead to searchable sets with room in their chains is NOT searched; its pairs become REVERSE members of the
 // chains of their target sets (rev_head / rev_next), which are thereby forced to be searched.
 constexpr int kChainWindow = 16;
-constexpr int kPrepSmemPairs = 4096;            // cover decided in shared memory up to this many pairs (else in global memory)
+constexpr int kPrepSmemPairs = 11000;           // cover decided in shared memory up to this many pairs (5 ints each: 215 KB; beyond: in global memory, ~3 us per pair)
 struct PrepLimits {
     int n_masks, n_dets;            // mask_idx in [0, n_masks), detection rows in [0, n_dets]
     long long out_capacity;         // out_off + n_src * n_dst <= out_capacity

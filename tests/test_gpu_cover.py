@@ -211,3 +211,22 @@ def test_cover_equals_directed_searches_at_full_size(cuda):
         outs.append([l for l in r.stdout.splitlines() if l.startswith('CRC')])
     assert len(outs[0]) == 2 and outs[0] == outs[1], outs
     assert int(outs[0][0].split()[-1]) > 10000
+
+
+def test_cover_with_more_pairs_than_the_shared_memory_path_holds(cuda):
+    """> 11 000 pairs: k2_prep_kernel decides the cover in global memory instead of shared memory; 5 800 frames of
+    two or three detections on a small island mask, every pair against the oracle."""
+    H, W = 48, 64
+    mask = _islands_mask(H, W, 31)
+    rng = np.random.default_rng(32)
+    fg = np.argwhere(mask)
+    frames = []
+    for t in range(5800):
+        n = 2 + (t % 3 == 0)
+        d = fg[rng.integers(0, len(fg), n)] + rng.integers(-1, 2, (n, 2)) * (rng.random((n, 1)) < 0.2)
+        d[:, 0] = np.clip(d[:, 0], 0, H - 1); d[:, 1] = np.clip(d[:, 1], 0, W - 1)
+        frames.append(d.astype(np.int32))
+    spec = _timelapse_pairs(frames, 1)
+    assert len(spec) > 11000
+    n = _run_and_check(cuda, mask, frames, spec, 25, 'many pairs')
+    assert n > 5000
