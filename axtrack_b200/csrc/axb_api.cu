@@ -264,11 +264,44 @@ int status_decode(axb_ctx* c, unsigned long long key, unsigned long long flags, 
     return rc;
 }
 
+// What K2 derives from the masks alone: the chunks of one host call share them (computed once on the first ctx).
+struct MaskProducts {
+    const uint32_t* tiles;
+    const int* comp_label;      // NULL: no cover
+    const int4* comp_ext;
+};
+
+bool cover_possible(int n_masks, int H, int W) {
+    static const bool no_reverse = getenv("AXB_K2_NO_REVERSE") != nullptr;
+    const size_t px = (size_t)n_masks * H * W;
+    return !no_reverse && (size_t)H * W < (1ull << 31) && px * 20 <= (4ull << 30);
+}
+
+// tiled masks + (when the cover can be used) their components, on stream s into the ctx's own buffers
+int mask_products(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W, bool want_components, cudaStream_t s,
+                  MaskProducts* out) {
+    const int Wp = (W + 31) / 32, TH = (H + 3) / 4;
+    int rc = grow(c, &c->k2_tiles, &c->k2_tiles_bytes, (size_t)n_masks * TH * Wp * 4 * sizeof(uint32_t));
+    if (rc != AXB_OK) return rc;
+    axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
+    c->launches += 1;
+    out->tiles = c->k2_tiles; out->comp_label = nullptr; out->comp_ext = nullptr;
+    if (want_components) {
+        const size_t px = (size_t)n_masks * H * W;
+        if ((rc = grow(c, &c->comp_label, &c->comp_label_bytes, px * sizeof(int))) != AXB_OK) return rc;
+        if ((rc = grow(c, &c->comp_ext, &c->comp_ext_bytes, px * sizeof(int4))) != AXB_OK) return rc;
+        axb::launch_k2_components(mask_bits_dev, n_masks, H, W, Wp, c->comp_label, c->comp_ext, s);
+        c->launches += 4;
+        out->comp_label = c->comp_label; out->comp_ext = c->comp_ext;
+    }
+    return AXB_OK;
+}
+
 int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
                            const int32_t* dets_yx_dev, int n_dets, const axb_pair_desc* pairs_dev, int n_pairs,
                            int total_src, int max_px,
                            int32_t* path_len_dev, uint8_t* unreachable_dev, float* wcost_dev, int64_t out_capacity,
-                           long long orig_base, void* stream) {
+                           long long orig_base, void* stream, const MaskProducts* shared = nullptr) {
     if (!c) return AXB_ERR_BAD_ARG;
     if (n_pairs < 0 || total_src < 0 || H <= 0 || W <= 0 || n_masks <= 0 || n_dets < 0 || out_capacity < 0)
         return bad_arg(c, "axb_cost_matrix_batch: bad size");
@@ -281,24 +314,18 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     int rc = ensure_k2(c, n_pairs, total_src);
     if (rc != AXB_OK) return rc;
     const int Wp = (W + 31) / 32, TH = (H + 3) / 4;
-    rc = grow(c, &c->k2_tiles, &c->k2_tiles_bytes, (size_t)n_masks * TH * Wp * 4 * sizeof(uint32_t));
-    if (rc != AXB_OK) return rc;
     const bool wide = max_px > axb::kFastMaxPx;
     if (wide && !c->k2_wide_scratch)
         AXB_CUDA(c, cudaMalloc((void**)&c->k2_wide_scratch, (size_t)c->k2_gen_ctas * axb::kWideCtasPerSm * axb::kGenScratchWordsWide * sizeof(uint32_t)));
-    axb::launch_k2_tiles(mask_bits_dev, n_masks, H, Wp, c->k2_tiles, s);
     // Cover (axb_search.cu k2_prep_kernel): pairs whose source frame is not searched are answered from their target
     // side; that needs the components of the masks.  Off for a single pair (nothing to share), for label arrays
     // beyond 4 GiB and with AXB_K2_NO_REVERSE (A/B timing, tests).
-    static const bool no_reverse = getenv("AXB_K2_NO_REVERSE") != nullptr;
-    const size_t px = (size_t)n_masks * H * W;
-    const bool cover = !no_reverse && n_pairs >= 2 && (size_t)H * W < (1ull << 31) && px * 20 <= (4ull << 30);
-    if (cover) {
-        if ((rc = grow(c, &c->comp_label, &c->comp_label_bytes, px * sizeof(int))) != AXB_OK) return rc;
-        if ((rc = grow(c, &c->comp_ext, &c->comp_ext_bytes, px * sizeof(int4))) != AXB_OK) return rc;
-        axb::launch_k2_components(mask_bits_dev, n_masks, H, W, Wp, c->comp_label, c->comp_ext, s);
-        c->launches += 4;
+    MaskProducts own;
+    if (!shared) {
+        if ((rc = mask_products(c, mask_bits_dev, n_masks, H, W, n_pairs >= 2 && cover_possible(n_masks, H, W), s, &own)) != AXB_OK) return rc;
+        shared = &own;
     }
+    const bool cover = n_pairs >= 2 && shared->comp_label != nullptr;
     const axb::K2Prep prep = prep_arrays(c);
     axb::launch_k2_prep(pairs_dev, n_pairs, prep, c->counters, n_masks, n_dets, (long long)out_capacity, total_src, cover ? 1 : 0,
                         c->status_dev + 1, s);
@@ -306,7 +333,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     axb::K2Params p;
     memset(&p, 0, sizeof p);
     p.mask_bits = mask_bits_dev; p.H = H; p.W = W; p.Wp = Wp;
-    p.mask_tiles = c->k2_tiles; p.TH = TH; p.TWp = 4 * Wp;
+    p.mask_tiles = shared->tiles; p.TH = TH; p.TWp = 4 * Wp;
     p.dets_yx = dets_yx_dev; p.pairs = pairs_dev; p.n_pairs = n_pairs;
     set_prep(p, prep, c);
     p.max_px = max_px; p.hash_smem = 0; p.sparse_words = axb::kSparseWords; p.path_len = path_len_dev; p.unreachable = unreachable_dev; p.wcost = wcost_dev;
@@ -314,7 +341,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     p.err_key = c->status_dev;
     p.trace_par = nullptr; p.trace_yx = nullptr; p.trace_len = nullptr;
     p.orig_base = orig_base;
-    p.comp_label = cover ? c->comp_label : nullptr; p.comp_ext = cover ? c->comp_ext : nullptr;
+    p.comp_label = cover ? shared->comp_label : nullptr; p.comp_ext = cover ? shared->comp_ext : nullptr;
     // In-grid off-mask detections (a few per cent on real data) need the all-levels kernel, one search latency each:
     // it takes them on a side stream while the level-0 kernels run (k2_classify_kernel).  AXB_K2_NO_EARLY: A/B timing.
     static const bool no_early = getenv("AXB_K2_NO_EARLY") != nullptr;
@@ -361,7 +388,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
         }
         if (early) AXB_CUDA(c, cudaStreamWaitEvent(s, c->ev_join, 0));      // one scratch set: the late list after the early one
         axb::launch_k2_general(p, gen_grid, s);
-        c->launches += 5;
+        c->launches += 4;
         AXB_CUDA(c, cudaGetLastError());
         static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;     // profiling aid: where the work items went
         if (dbg) {
@@ -392,7 +419,7 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     }
     if (early) AXB_CUDA(c, cudaStreamWaitEvent(s, c->ev_join, 0));          // one scratch set: the late list after the early one
     axb::launch_k2_general(p, gen_grid, s);
-    c->launches += 5;
+    c->launches += 4;
     AXB_CUDA(c, cudaGetLastError());
     static const bool dbg = getenv("AXB_K2_DEBUG") != nullptr;
     if (dbg) {
@@ -481,16 +508,21 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
     if ((rc = axb_pack_mask(c, c->st_mask, n_masks, H, W, c->st_bits, s)) != AXB_OK) return rc;
 
     // Chunks of frame pairs: the searches of chunk k+1 (other scratch set, other stream) fill the SMs as chunk k
-    // drains, and the copy stream takes chunk k's matrices to the host meanwhile.  Every chunk costs a launch-group
-    // tail (~1 ms) and the last chunk's copy is exposed, so n ~ sqrt(copy time / tail): one chunk up to ~100 MB of
-    // results (configs[1]: 44 MB, measured faster unchunked), 5 for the 1.36 GB of configs[2]; a chunk holds at least
-    // four full rounds of searches.
+    // drains, and the copy stream takes chunk k's matrices to the host meanwhile.  Tiles and components of the masks
+    // are computed once for all chunks.  One chunk up to 320 MB of results (configs[1]: 44 MB, measured faster
+    // unchunked), up to 8 beyond (configs[2], 1.36 GB: unchunked 97.7 ms, 5 equal chunks 87.7, 8 shrinking chunks
+    // 78.9 ms end to end against 72.3 ms on the device).
+    constexpr double kChunkRatio = 0.8;
     static const bool no_chunks = getenv("AXB_HOST_NO_CHUNKS") != nullptr;
     const double out_mb = (double)total_out * (wcost_host ? 9.0 : 5.0) / (1 << 20);
-    int n_chunks = (int)std::min<long long>(std::min<long long>(8, (long long)(std::sqrt(out_mb / 64.0) + 0.5)),
-                                            total_src / (4LL * c->num_sms * axb::kSparseCtasPerSm));
+    int n_chunks = (int)std::min<long long>(8, (long long)(out_mb / 160.0));
+    if (const char* e = getenv("AXB_HOST_CHUNKS")) n_chunks = std::max(1, std::min(8, atoi(e)));      // experiments
+    // the smallest (last) chunk still holds two full rounds of searches
+    while (n_chunks > 1 && total_src * (1.0 - kChunkRatio) * std::pow(kChunkRatio, n_chunks - 1) / (1.0 - std::pow(kChunkRatio, n_chunks)) < 2.0 * c->num_sms * axb::kSparseCtasPerSm) --n_chunks;
     if (n_chunks < 2 || no_chunks || total_out <= 0) n_chunks = 1;
     axb_ctx* ctxs[2] = {c, c};
+    MaskProducts shared;               // tiles and components once for all chunks, ahead of the fork
+    if ((rc = mask_products(c, c->st_bits, n_masks, H, W, n_pairs >= 2 && cover_possible(n_masks, H, W), s, &shared)) != AXB_OK) return rc;
     if (n_chunks > 1) {
         if (!c->alt && (rc = axb_create(c->device, &c->alt)) != AXB_OK) return rc;
         if (!c->copy_stream) AXB_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
@@ -505,8 +537,14 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
         int p0 = 0;
         for (int k = 0; k < n_chunks; ++k) {
             int p1 = n_pairs;
-            if (k + 1 < n_chunks) {            // cut where the running source count passes k+1 shares
-                const long long want = total_src * (k + 1) / n_chunks;
+            if (k + 1 < n_chunks) {
+                // Shrinking chunks (each 0.8 of the one before): a chunk's copy (~54 GB/s) hides behind the searches of
+                // the next one (~19 GB/s of results on configs[2]) as long as that one is at least a third as large,
+                // and the copy of the LAST chunk is exposed -- so it should be the smallest (measured on configs[2]:
+                // 5 equal chunks 87.7 ms, 8 chunks of ratio 0.8 78.9 ms, unchunked 97.7 ms end to end).
+                static const double r = getenv("AXB_HOST_CHUNK_RATIO") ? atof(getenv("AXB_HOST_CHUNK_RATIO")) : kChunkRatio;
+                const double frac = r >= 0.999 ? (double)(k + 1) / n_chunks : (1.0 - std::pow(r, k + 1)) / (1.0 - std::pow(r, n_chunks));
+                const long long want = (long long)(total_src * frac);
                 p1 = (int)(std::lower_bound(src_prefix.begin(), src_prefix.end(), want) - src_prefix.begin());
                 p1 = std::min(std::max(p1, p0), n_pairs);
             }
@@ -515,7 +553,7 @@ int axb_cost_matrix_batch_host(axb_ctx* c, const uint8_t* masks_host, int n_mask
             cudaStream_t cs = cc->own_stream;
             rc = cost_matrix_batch_impl(cc, c->st_bits, n_masks, H, W, c->st_dets, n_dets, c->st_pairs + p0, p1 - p0,
                                         (int)(src_prefix[p1] - src_prefix[p0]), max_px, c->st_plen, c->st_unr,
-                                        wcost_host ? c->st_wc : nullptr, (int64_t)total_out, src_prefix[p0], cs);
+                                        wcost_host ? c->st_wc : nullptr, (int64_t)total_out, src_prefix[p0], cs, &shared);
             if (rc != AXB_OK) { if (cc != c) c->err = cc->err; return rc; }
             long long lo = total_out, hi = 0;
             for (int i = p0; i < p1; ++i) {
