@@ -164,7 +164,8 @@ int axb_create(int device, axb_ctx** out) {
     if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return AXB_ERR_CUDA;
     axb_ctx* c = new axb_ctx();
     c->device = device;
-    if (cudaSetDevice(device) != cudaSuccess) { delete c; return AXB_ERR_CUDA; }
+    DeviceGuard guard(device);          // the caller's current device is restored on every return path
+    if (guard.err != cudaSuccess) { delete c; return AXB_ERR_CUDA; }
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete c; return AXB_ERR_CUDA; }
     c->num_sms = prop.multiProcessorCount;
@@ -181,7 +182,7 @@ int axb_create(int device, axb_ctx** out) {
 
 void axb_destroy(axb_ctx* c) {
     if (!c) return;
-    cudaSetDevice(c->device);
+    DeviceGuard guard(c->device);
     cudaDeviceSynchronize();
     if (c->alt) { axb_destroy(c->alt); c->alt = nullptr; }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
