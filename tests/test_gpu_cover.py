@@ -230,3 +230,51 @@ def test_cover_with_more_pairs_than_the_shared_memory_path_holds(cuda):
     assert len(spec) > 11000
     n = _run_and_check(cuda, mask, frames, spec, 25, 'many pairs')
     assert n > 5000
+
+
+def test_cost_matrix_batch_under_graph_capture(cuda):
+    """axb_cost_matrix_batch forks the all-levels searches of off-mask detections onto a ctx-owned side stream and
+    joins it back before its last launch: to the caller it is ONE call ordered on `stream`, so it can be captured
+    into a CUDA graph (after one warm-up call that sizes the scratch) and replayed on new detections."""
+    from axtrack_b200 import ops
+    torch = cuda
+    H, W = 400, 520
+    mask = synth.make_mask(H, W, 3, pitch=(50, 110), width=(4, 9)).astype(bool)
+    tracks = [t.astype(np.int32) for t in synth.make_tracks(mask, 40, 6, 3, off_mask_frac=0.15)]
+    n = min(len(t) for t in tracks)
+    tracks = [t[:n] for t in tracks]                       # fixed shapes: the graph is replayed on other coordinates
+    offs = np.arange(7) * n
+    spec = _timelapse_pairs(tracks, 1)
+    pairs, total, _ = ops.make_pairs([(mk, int(offs[a]), n, int(offs[b]), n) for mk, a, b in spec])
+    dev = torch.device('cuda', 0)
+    bits = ops.pack_mask(torch.from_numpy(mask.astype(np.uint8)).to(dev))
+    dets = torch.from_numpy(np.concatenate(tracks)).to(dev)
+    pd = torch.from_numpy(pairs.view(np.uint8).reshape(-1).copy()).to(dev)
+    out = (torch.empty(total, dtype=torch.int32, device=dev), torch.empty(total, dtype=torch.uint8, device=dev),
+           torch.empty(total, dtype=torch.float32, device=dev))
+    ops.cost_matrix_batch(bits, W, dets, pairs, 150, out=out, pairs_dev=pd)          # warm-up: allocations happen here
+    torch.cuda.synchronize()
+    want = [o.clone() for o in out]
+    side = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        ops.cost_matrix_batch(bits, W, dets, pairs, 150, out=out, pairs_dev=pd)
+    for o in out:
+        o.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    for a, b in zip(out, want):
+        assert torch.equal(a, b)
+    # other coordinates, same graph: frames rolled by one
+    rolled = np.concatenate(tracks[1:] + tracks[:1])
+    dets.copy_(torch.from_numpy(rolled).to(dev))
+    g.replay()
+    torch.cuda.synchronize()
+    ops.raise_status()
+    pl, un = out[0].cpu().numpy(), out[1].cpu().numpy()
+    fr = tracks[1:] + tracks[:1]
+    for (mk, a, b), p in zip(spec, pairs):
+        o = int(p['out_off'])
+        ref = oracle.cost_matrix_rule(mask, fr[a], fr[b], 150)
+        assert np.array_equal(pl[o:o + n * n].reshape(n, n), ref[0].reshape(n, n)), (a, b)
+        assert np.array_equal(un[o:o + n * n].reshape(n, n), ref[1].reshape(n, n)), (a, b)
