@@ -287,6 +287,9 @@ class Job:
         if self.world > 1:
             tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
             ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+            every = [torch.zeros_like(t) for _ in range(self.world)]
+            dist.all_gather(every, t)
+            self.rank_ms = [float(e[0]) / steps for e in every]      # each rank's own device time per step (the step is their max)
             return float(tm[0]), float(ts[1]), launches, res
         return ms, float(len(res.keys)), launches, res
 
@@ -560,6 +563,8 @@ def run_b200(args, wl):
                                 parallelism=f'one timelapse, timepoint shards x{world} (sharding.associate_sharded), ' + par,
                                 gathered_pairs_verified=gathered_pairs, l2='flushed between timed steps (256 MiB write)'),
                     e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu, strong_c4=strong)
+        if getattr(job, 'rank_ms', None):
+            line['rank_ms_per_step'] = [round(v, 4) for v in job.rank_ms]     # ms_per_step is their maximum
         emit(line)
     if world > 1:
         dist.destroy_process_group()
