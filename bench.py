@@ -343,6 +343,7 @@ def run_b200(args, wl):
     ctx = ops.get_context(dev)
     sampler = ClockSampler(local) if rank == 0 else None
     ms, total_pairs, launches, res = job.timed(args.steps, args.warmup, flush, ctx, sampler)
+    rank_ms = getattr(job, 'rank_ms', None)
     clocks = sampler.stop() if rank == 0 else None
     value = total_pairs * args.steps / (ms * 1e-3)
     gathered_pairs = job.verify_gather()
@@ -563,8 +564,8 @@ def run_b200(args, wl):
                                 parallelism=f'one timelapse, timepoint shards x{world} (sharding.associate_sharded), ' + par,
                                 gathered_pairs_verified=gathered_pairs, l2='flushed between timed steps (256 MiB write)'),
                     e2e=e2e, gpu_launches=int(launches), clocks=clocks, roofline=roofline, cpu_baseline=cpu, strong_c4=strong)
-        if getattr(job, 'rank_ms', None):
-            line['rank_ms_per_step'] = [round(v, 4) for v in job.rank_ms]     # ms_per_step is their maximum
+        if rank_ms:
+            line['rank_ms_per_step'] = [round(v, 4) for v in rank_ms]     # ms_per_step is their maximum
         emit(line)
     if world > 1:
         dist.destroy_process_group()
