@@ -23,7 +23,7 @@ MAX_PX = 1023
 
 #: every symbol include/axtrack_b200.h declares
 SYMBOLS = ('axb_create', 'axb_destroy', 'axb_last_error', 'axb_version', 'axb_launch_count',
-           'axb_mask_words', 'axb_pack_mask', 'axb_pack_weights', 'axb_cost_matrix_batch',
+           'axb_mask_words', 'axb_pack_mask', 'axb_pack_weights', 'axb_prepare_masks', 'axb_cost_matrix_batch',
            'axb_cost_matrix', 'axb_cost_matrix_batch_host', 'axb_cost_matrix_host',
            'axb_decode_nms', 'axb_decode_nms_host', 'axb_transition_cost_batch', 'axb_trace_paths', 'axb_feature_hist',
            'axb_feature_hist_frames', 'axb_vis_sim',
@@ -70,6 +70,8 @@ def load():
     L.axb_pack_mask.argtypes = [vp, vp, ci, ci, ci, vp, vp]
     L.axb_pack_weights.restype = ci
     L.axb_pack_weights.argtypes = [vp, vp, ci, ci, ci, vp, vp]
+    L.axb_prepare_masks.restype = ci
+    L.axb_prepare_masks.argtypes = [vp, vp, ci, ci, ci, vp]
     L.axb_cost_matrix_batch.restype = ci
     L.axb_cost_matrix_batch.argtypes = [vp, vp, ci, ci, ci, vp, ci, vp, ci, ci, ci, vp, vp, vp, ctypes.c_int64, vp]
     L.axb_cost_matrix.restype = ci

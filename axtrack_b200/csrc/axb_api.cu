@@ -39,6 +39,8 @@ struct axb_ctx {
     int* comp_label = nullptr;        size_t comp_label_bytes = 0;      // mask components (axb_components.cu)
     int4* comp_ext = nullptr;         size_t comp_ext_bytes = 0;
     int dense_stride = 0;
+    // axb_prepare_masks: tiles / components of these mask bits are ready for the next axb_cost_matrix_batch (one shot)
+    const uint32_t* prep_bits = nullptr;   int prep_n_masks = 0, prep_H = 0, prep_W = 0;   bool prep_components = false;
     int* early_list = nullptr;        size_t early_list_bytes = 0;      // in-grid off-mask detections: the all-levels kernel runs them beside the level-0 kernels
     cudaStream_t side_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -322,6 +324,13 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
     // side; that needs the components of the masks.  Off for a single pair (nothing to share), for label arrays
     // beyond 4 GiB and with AXB_K2_NO_REVERSE (A/B timing, tests).
     MaskProducts own;
+    if (!shared && c->prep_bits == mask_bits_dev && c->prep_n_masks == n_masks && c->prep_H == H && c->prep_W == W) {
+        own.tiles = c->k2_tiles;                 // axb_prepare_masks ran on this stream for exactly these bits
+        own.comp_label = c->prep_components ? c->comp_label : nullptr;
+        own.comp_ext = c->prep_components ? c->comp_ext : nullptr;
+        shared = &own;
+    }
+    c->prep_bits = nullptr;                      // one shot
     if (!shared) {
         if ((rc = mask_products(c, mask_bits_dev, n_masks, H, W, n_pairs >= 2 && cover_possible(n_masks, H, W), s, &own)) != AXB_OK) return rc;
         shared = &own;
@@ -436,6 +445,21 @@ int cost_matrix_batch_impl(axb_ctx* c, const uint32_t* mask_bits_dev, int n_mask
 }  // namespace
 
 extern "C" {
+
+int axb_prepare_masks(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W, void* stream) {
+    if (!c) return AXB_ERR_BAD_ARG;
+    if (!mask_bits_dev) { c->prep_bits = nullptr; return AXB_OK; }      // discard what an earlier call prepared
+    if (H <= 0 || W <= 0 || n_masks <= 0) return bad_arg(c, "axb_prepare_masks: bad size");
+    AXB_ON_DEVICE(c);
+    c->prep_bits = nullptr;
+    MaskProducts mp;
+    const bool comps = cover_possible(n_masks, H, W);
+    const int rc = mask_products(c, mask_bits_dev, n_masks, H, W, comps, (cudaStream_t)stream, &mp);
+    if (rc != AXB_OK) return rc;
+    AXB_CUDA(c, cudaGetLastError());
+    c->prep_bits = mask_bits_dev; c->prep_n_masks = n_masks; c->prep_H = H; c->prep_W = W; c->prep_components = comps;
+    return AXB_OK;
+}
 
 int axb_cost_matrix_batch(axb_ctx* c, const uint32_t* mask_bits_dev, int n_masks, int H, int W,
                           const int32_t* dets_yx_dev, int n_dets, const axb_pair_desc* pairs_dev, int n_pairs,

@@ -60,6 +60,21 @@ def pack_mask(mask):
     return bits
 
 
+def prepare_masks(mask_bits, W):
+    """Optional: tile words and components of ``mask_bits`` (from pack_mask) ahead of the next ``cost_matrix_batch`` on
+    this device, which then skips that work -- call it before a host synchronisation the pair list depends on."""
+    mask_bits = _need_cuda(mask_bits, 'mask_bits', torch.int32)
+    n_masks, H, _ = mask_bits.shape
+    ctx = get_context(mask_bits.device)
+    ctx.check(ctx.lib.axb_prepare_masks(ctx.handle, mask_bits.data_ptr(), n_masks, H, int(W), _stream(mask_bits.device)))
+
+
+def discard_prepared_masks(device=None):
+    """Drop what ``prepare_masks`` left for the next ``cost_matrix_batch`` (when that call is not going to happen)."""
+    ctx = get_context(device)
+    ctx.check(ctx.lib.axb_prepare_masks(ctx.handle, None, 0, 0, 0, None))
+
+
 def pack_weights(weights):
     """float32 CUDA weight grid(s) as pyastar2d.astar_path takes them -> packed mask bits.
     Weight errors (min < 1: astar_wrapper.py:35-37) surface in ``raise_status``."""
@@ -107,6 +122,8 @@ def cost_matrix_batch(mask_bits, W, dets_yx, pairs, max_px=500, want_cost=True, 
             pairs_dev.data_ptr(), n_pairs, total_src, int(max_px),
             path_len.data_ptr(), unreach.data_ptr(), wcost.data_ptr() if wcost is not None else None,
             cap_out, _stream(dev)))
+    else:
+        discard_prepared_masks(dev)      # nothing to search: products of prepare_masks must not outlive this call
     return path_len[:total], unreach[:total], (wcost[:total] if wcost is not None else None), pairs
 
 

@@ -84,6 +84,16 @@ class Association:
         return self._host
 
 
+_pinned = {}
+
+
+def _pinned_counts(T, device):
+    key = (torch.device(device).index, int(T))
+    if key not in _pinned:
+        _pinned[key] = torch.empty(int(T), dtype=torch.int32).pin_memory()
+    return _pinned[key]
+
+
 def associate_frames(Y, tile_yx, mask, max_px=500, max_num_misses=1, tilesize=512, conf_thr=0.55,
                      nms_dist=23, cap=None, mask_of_frame=None, want_cost=True, want_pre=False,
                      mask_bits=None, t0=0, out_alloc=None):
@@ -100,10 +110,23 @@ def associate_frames(Y, tile_yx, mask, max_px=500, max_num_misses=1, tilesize=51
     if mask_bits is None:
         mask_bits = ops.pack_mask(mask)
     W = mask.shape[-1]
-    n_out = det['n_out'].cpu().numpy()          # the one host sync of the path: T int32
-    ops.raise_status(device=Y.device)
-    keys = frame_pair_keys(T, max_num_misses, t0)
-    pairs, total, _ = build_pairs(n_out, cap, keys, mask_of_frame)
-    out = out_alloc(total, pairs) if out_alloc is not None else None
-    pl, un, wc, _ = ops.cost_matrix_batch(mask_bits, W, det['yx'].view(-1, 2), pairs, max_px, want_cost, out=out)
+    # the one host sync of the path: T int32 counts.  They are copied to pinned memory first; the tiles / components of
+    # the masks are queued BEHIND that copy, so the GPU derives them while the host builds the pair list.
+    pin = _pinned_counts(T, Y.device)
+    pin.copy_(det['n_out'], non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(Y.device))
+    if T >= 3:                                  # >= 2 frame pairs
+        ops.prepare_masks(mask_bits, W)
+    try:
+        ev.synchronize()
+        n_out = pin.numpy().copy()
+        ops.raise_status(device=Y.device)
+        keys = frame_pair_keys(T, max_num_misses, t0)
+        pairs, total, _ = build_pairs(n_out, cap, keys, mask_of_frame)
+        out = out_alloc(total, pairs) if out_alloc is not None else None
+        pl, un, wc, _ = ops.cost_matrix_batch(mask_bits, W, det['yx'].view(-1, 2), pairs, max_px, want_cost, out=out)
+    except BaseException:
+        ops.discard_prepared_masks(Y.device)
+        raise
     return Association(det, n_out, keys, pairs, pl, un, wc, ctx.launches - l0)

@@ -107,6 +107,16 @@ int axb_pack_weights(axb_ctx* ctx, const float* weights_dev, int n_masks, int H,
  * a pair with a negative count, detections outside [0, n_dets], mask_idx outside [0, n_masks) or
  * an output block outside [0, out_capacity) gets no work and sets AXB_ERR_BAD_ARG in axb_status,
  * as does a total_src smaller than the pairs' sources (then nothing runs). */
+/* Optional: what axb_cost_matrix_batch derives from the masks alone (8x4-pixel tile words, mask components for the
+ * cover) computed AHEAD of it, e.g. while the host still waits for the detection counts it builds the pair
+ * descriptors from (AxonDetections.py:553-566 reads len(dets) per frame).  One shot: the NEXT axb_cost_matrix_batch
+ * on this ctx with the same pointer and sizes uses the products and skips that work; any other call in between
+ * discards them, and so does axb_prepare_masks(ctx, NULL, ...) (do that when the batch call is not going to
+ * happen: the products are keyed by the pointer, not by the mask's contents).  Same stream as that call; the bits
+ * must not change in between.  No reference counterpart (the reference has no such stage); results are identical
+ * with and without it. */
+int axb_prepare_masks(axb_ctx* ctx, const uint32_t* mask_bits_dev, int n_masks, int H, int W, void* stream);
+
 int axb_cost_matrix_batch(axb_ctx* ctx,
                           const uint32_t* mask_bits_dev, int n_masks, int H, int W,
                           const int32_t* dets_yx_dev, int n_dets,

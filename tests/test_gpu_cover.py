@@ -278,3 +278,56 @@ def test_cost_matrix_batch_under_graph_capture(cuda):
         ref = oracle.cost_matrix_rule(mask, fr[a], fr[b], 150)
         assert np.array_equal(pl[o:o + n * n].reshape(n, n), ref[0].reshape(n, n)), (a, b)
         assert np.array_equal(un[o:o + n * n].reshape(n, n), ref[1].reshape(n, n)), (a, b)
+
+
+def test_prepare_masks_is_one_shot_and_changes_nothing(cuda):
+    """axb_prepare_masks ahead of axb_cost_matrix_batch: same results; the products are used once, for the same
+    pointer and sizes only, and never for another mask."""
+    from axtrack_b200 import ops
+    torch = cuda
+    H, W = 260, 300
+    frames = None
+    dev = torch.device('cuda', 0)
+    ctx = ops.get_context(dev)
+    mask_a, mask_b = _islands_mask(H, W, 41), _islands_mask(H, W, 42)
+    frames = _frames_on(mask_a | mask_b, 5, 30, 43, off_frac=0.2)
+    offs = np.concatenate([[0], np.cumsum([len(f) for f in frames])])
+    spec = _timelapse_pairs(frames, 1)
+    pairs, total, _ = ops.make_pairs([(mk, int(offs[a]), len(frames[a]), int(offs[b]), len(frames[b])) for mk, a, b in spec])
+    dets = torch.from_numpy(np.concatenate(frames).astype(np.int32)).to(dev)
+    bits = ops.pack_mask(torch.from_numpy(mask_a.astype(np.uint8)).to(dev))
+
+    def run():
+        pl, un, wc, _ = ops.cost_matrix_batch(bits, W, dets, pairs, 60)
+        ops.raise_status()
+        return pl.clone(), un.clone(), wc.clone()
+
+    plain = run()
+    l0 = ctx.launches
+    run()
+    n_plain = ctx.launches - l0
+    ops.prepare_masks(bits, W)
+    l0 = ctx.launches
+    prepared = run()
+    n_prepared = ctx.launches - l0
+    assert n_prepared == n_plain - 5                       # tile words + the four component kernels ran ahead
+    for a, b in zip(plain, prepared):
+        assert torch.equal(a, b)
+    l0 = ctx.launches
+    run()                                                  # one shot: the next call derives them again
+    assert ctx.launches - l0 == n_plain
+    # prepared for mask A, then the SAME buffer is given mask B's bits via another pointer of the same size: not used
+    bits_b = ops.pack_mask(torch.from_numpy(mask_b.astype(np.uint8)).to(dev))
+    ops.prepare_masks(bits, W)
+    pl_b, un_b, _, _ = ops.cost_matrix_batch(bits_b, W, dets, pairs, 60)
+    ops.raise_status()
+    for (mk, a, b), p in zip(spec, pairs):
+        o, ns, nd = int(p['out_off']), int(p['n_src']), int(p['n_dst'])
+        ref = oracle.cost_matrix_rule(mask_b, frames[a], frames[b], 60)
+        assert np.array_equal(pl_b[o:o + ns * nd].cpu().numpy().reshape(ns, nd), ref[0].reshape(ns, nd))
+    # discarded explicitly
+    ops.prepare_masks(bits, W)
+    ops.discard_prepared_masks(dev)
+    l0 = ctx.launches
+    run()
+    assert ctx.launches - l0 == n_plain
