@@ -110,18 +110,18 @@ def associate_frames(Y, tile_yx, mask, max_px=500, max_num_misses=1, tilesize=51
     if mask_bits is None:
         mask_bits = ops.pack_mask(mask)
     W = mask.shape[-1]
-    # the one host sync of the path: T int32 counts.  They are copied to pinned memory first; the tiles / components of
-    # the masks are queued BEHIND that copy, so the GPU derives them while the host builds the pair list.
+    # the one host sync of the path: T int32 counts, through pinned memory.  The tiles / components of the masks are
+    # queued right after it, so the GPU derives them while the host builds the pair list and its device copy.
     pin = _pinned_counts(T, Y.device)
     pin.copy_(det['n_out'], non_blocking=True)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(Y.device))
+    ev.synchronize()
+    n_out = pin.numpy().copy()
+    ops.raise_status(device=Y.device)           # (synchronises the stream: before anything else is queued on it)
     if T >= 3:                                  # >= 2 frame pairs
         ops.prepare_masks(mask_bits, W)
     try:
-        ev.synchronize()
-        n_out = pin.numpy().copy()
-        ops.raise_status(device=Y.device)
         keys = frame_pair_keys(T, max_num_misses, t0)
         pairs, total, _ = build_pairs(n_out, cap, keys, mask_of_frame)
         out = out_alloc(total, pairs) if out_alloc is not None else None
