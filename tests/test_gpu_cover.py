@@ -331,3 +331,15 @@ def test_prepare_masks_is_one_shot_and_changes_nothing(cuda):
     l0 = ctx.launches
     run()
     assert ctx.launches - l0 == n_plain
+
+
+def test_cover_with_more_candidates_than_one_pass_holds(cuda):
+    """~200 detections per frame inside one radius: a searched detection has up to 800 in-range candidates over its
+    forward and reverse members, more than the target hash of one pass holds (320), so the search repeats in passes;
+    islands and off-mask detections keep the directed and all-levels fallbacks busy in the later passes too."""
+    H, W = 110, 150
+    mask = _islands_mask(H, W, 51)
+    mask[40:70, 20:130] = True                              # a large blob: most detections see each other
+    frames = _frames_on(mask, 5, 200, 52, off_frac=0.15)
+    n = _run_and_check(cuda, mask, frames, _timelapse_pairs(frames, 1), 90, 'multi-pass')
+    assert n > 100000
